@@ -1,0 +1,170 @@
+/*
+ * melissa_b200 -- C ABI of the B200-native variational-Bayes hot path of Melissa.
+ *
+ * This is the drop-in boundary for the reference's `melissa()` /
+ * `melissa_inner()` (reference R/melissa_vb.R:86-219 and :232-529).  The
+ * reference is pure R and has no FFI of its own; these are the symbols an R
+ * `.Call` / `.C` glue or any other host binds.  Plain
+ * pointers and sizes only: no R, torch or C++ types cross this boundary, no
+ * C++ exception leaves it.  Every function returns 0 on success and a
+ * non-zero status on failure, with a message in melissa_last_error().
+ *
+ * Index conventions: everything is 0-based.  A "pair" is one covered
+ * (cell, region) combination, i.e. one non-NA element X[[n]][[m]] of the
+ * reference's nested input list (R/melissa_vb.R:11-17, :119-121).  Pairs are
+ * passed cell-major (all pairs of cell 0, then cell 1, ...), regions ascending
+ * inside a cell -- the order `which(!is.na(X[[n]]))` produces.
+ * Array layouts on the way out are R's (column-major) so the glue can hand
+ * the buffers to `array()` / `matrix()` unchanged.
+ */
+#ifndef MELISSA_B200_H
+#define MELISSA_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct melissa_handle melissa_handle;
+
+/* status codes */
+#define MELISSA_OK 0
+#define MELISSA_ERR_ARG 1      /* bad argument (mirrors the reference's assert_that / stop) */
+#define MELISSA_ERR_CUDA 2     /* CUDA runtime failure */
+#define MELISSA_ERR_STATE 3    /* call out of order */
+
+/* flags written by melissa_vb_run / melissa_vb_flags */
+#define MELISSA_FLAG_LB_DECREASED 1   /* warning("Warning: Lower bound decreases!")  R/melissa_vb.R:495-497 */
+#define MELISSA_FLAG_NOT_CONVERGED 2  /* warning("VB did not converge!")             R/melissa_vb.R:511-513 */
+
+/* basis kinds (BPRMeth basis objects; only the RBF object is pinned) */
+#define MELISSA_BASIS_RBF 1
+
+/* Message of the last failure on the calling thread ("" if none). */
+const char *melissa_last_error(void);
+
+/* ABI version of the loaded library. */
+int melissa_abi_version(void);
+
+/*
+ * Pack the observations once (replaces init_design_matrix / extract_y /
+ * region_ind / cell_ind / HH construction: R/utils.R:64-97,
+ * R/melissa_vb.R:119-131, :254-259).  Copies the host arrays to `device`,
+ * builds the region-major index and the per-pair H^T H; the design matrices H
+ * are never materialised (the RBF basis is re-evaluated in-kernel).
+ *
+ *   n_cells, n_regions   N and M of THIS shard (cells may be a shard of a larger job)
+ *   n_pairs              P, number of covered (cell, region) pairs
+ *   pair_ptr[P+1]        CpG offsets of each pair into x / y
+ *   pair_cell[P]         cell of each pair, non-decreasing (cell-major)
+ *   pair_region[P]       region of each pair, strictly increasing inside a cell
+ *   x[nnz]               CpG locations scaled to [-1, 1] (column 1 of the region matrix)
+ *   y[nnz]               methylation state, 0 or 1       (column 2)
+ *   basis_kind           MELISSA_BASIS_RBF
+ *   n_basis              basis$M (number of RBFs; D = n_basis + 1; 0 = mean-rate model)
+ *   mus[n_basis], gamma  basis$mus, basis$gamma
+ *
+ * Errors mirror the reference: a cell without any covered region fails like
+ * stop("No coverage across all regions. ...") (R/utils.R:69-71); a region no
+ * cell covers is rejected (the reference's .add_func(NULL) would fail,
+ * R/melissa_vb.R:368-370) unless allow_empty_regions != 0 (cell shards).
+ */
+int melissa_pack(int32_t n_cells, int32_t n_regions, int64_t n_pairs,
+                 const int64_t *pair_ptr, const int32_t *pair_cell, const int32_t *pair_region,
+                 const double *x, const uint8_t *y,
+                 int32_t basis_kind, int32_t n_basis, const double *mus, double gamma,
+                 int32_t device, int32_t allow_empty_regions, melissa_handle **out);
+
+/* Release every device and host resource behind the handle (NULL is a no-op). */
+int melissa_free(melissa_handle *h);
+
+/*
+ * One complete VB fit on one GPU: melissa_inner (R/melissa_vb.R:232-529).
+ * All buffers are HOST memory owned by the caller.
+ *
+ *   K                  number of clusters
+ *   w0[M*D*K]          initial means, R array dim c(M, D, K), column-major
+ *   delta_0[K]         Dirichlet prior
+ *   alpha_0, beta_0    Gamma prior; beta_0 = NaN means the reference default
+ *                      sqrt(alpha_0 + M*D/2)                      (:271-273)
+ *   vb_max_iter        the loop runs i = 2 .. vb_max_iter          (:309)
+ *   epsilon_conv       stop when |LB - LB_prev| < epsilon_conv     (:499-501)
+ *   lb_every           lower bound every lb_every-th i and at vb_max_iter (10 in the reference, :458)
+ *  outputs (any may be NULL to skip):
+ *   W[M*D*K]           posterior means, dim c(M, D, K)
+ *   W_Sigma[K*M*D*D]   posterior covariances; block (k, m) at ((k*M)+m)*D*D, each D x D
+ *   r_nk[N*K]          responsibilities, dim c(N, K) column-major
+ *   delta, alpha, beta, pi_k   each [K]
+ *   lb[lb_cap]         lower bounds; lb[0] = -Inf as in the reference (:242); NOT yet minus log(K!)
+ *   n_lb               entries written to lb
+ *   n_iter             last i executed
+ *   flags              MELISSA_FLAG_* bits
+ */
+int melissa_vb_run(melissa_handle *h, int32_t K, const double *w0, const double *delta_0,
+                   double alpha_0, double beta_0, int32_t vb_max_iter, double epsilon_conv,
+                   int32_t lb_every,
+                   double *W, double *W_Sigma, double *r_nk, double *delta, double *alpha,
+                   double *beta, double *pi_k, double *lb, int32_t lb_cap, int32_t *n_lb,
+                   int32_t *n_iter, int32_t *flags);
+
+/*
+ * Step-wise interface (what melissa_vb_run is built from).  A host that shards
+ * cells over several GPUs (one process per GPU) drives these and all-reduces
+ * the reduction buffer between the phases; see INTEGRATION.md.
+ *
+ *   melissa_vb_begin     state set-up + first E[z] sweep   (R/melissa_vb.R:262-302)
+ *   melissa_vb_phase_a   responsibilities (:330-331) and this shard's
+ *                        r-weighted sufficient statistics (:368-373 sums)
+ *                        -> reduction buffer  [all-reduce SUM it here]
+ *   melissa_vb_phase_b   q(w) solves, beta/delta/E[log pi] updates (:368-392,
+ *                        :443-451), E[z] refresh sweep (:418-435); with_lb != 0
+ *                        also accumulates this shard's lb_pz_qz (:469-473)
+ *                        -> lb buffer            [all-reduce SUM it here]
+ *   melissa_vb_lower_bound  assembles LB (:475-492), returns it to the host
+ *
+ * n_cells_total is N of the whole job (pi_k's denominator, :338).
+ * `stream` is a cudaStream_t (NULL = default stream); the caller's collective
+ * must be ordered on the same stream.
+ */
+int melissa_vb_begin(melissa_handle *h, int32_t K, const double *w0, const double *delta_0,
+                     double alpha_0, double beta_0, int64_t n_cells_total, void *stream);
+int melissa_vb_phase_a(melissa_handle *h);
+int melissa_vb_phase_b(melissa_handle *h, int32_t with_lb);
+int melissa_vb_lower_bound(melissa_handle *h, double *lb_out);
+
+/* Device pointers + lengths (in doubles) of the two buffers a multi-GPU host all-reduces. */
+int melissa_vb_reduce_buffer(melissa_handle *h, void **dev_ptr, int64_t *n_doubles);
+int melissa_vb_lb_buffer(melissa_handle *h, void **dev_ptr, int64_t *n_doubles);
+
+/* Copy the current state to host buffers (same layouts as melissa_vb_run; NULL skips). */
+int melissa_vb_fetch(melissa_handle *h, double *W, double *W_Sigma, double *r_nk,
+                     double *delta, double *alpha, double *beta, double *pi_k);
+
+/* Per-pair H^T E[z] of the last sweep, [P * D] row-major per pair (diagnostic / parity tests). */
+int melissa_vb_fetch_HtEz(melissa_handle *h, double *out);
+
+/* Block until all work queued on the handle's stream is done. */
+int melissa_sync(melissa_handle *h);
+
+/* Number of kernels this handle has launched so far (bench.py's gpu_launches). */
+int64_t melissa_launch_count(const melissa_handle *h);
+
+/*
+ * Imputation pass (reference impute_test_met with basis = NULL, is_predictive =
+ * TRUE: R/utils.R:225-284): pred[i] = round(sum_k r_nk[n,k] * Phi(h(x_i) . W[m,,k]), 3)
+ * for held-out CpGs given as the same kind of cell-major pair list (cells
+ * without held-out regions simply have no pair).  Stand-alone: takes the fitted
+ * W (dim c(M, D, K)) and r_nk (dim c(N, K)) of a melissa object, column-major,
+ * as HOST buffers; pred[nnz] is a HOST buffer.
+ */
+int melissa_impute(int32_t n_cells, int32_t n_regions, int32_t K, int32_t basis_kind, int32_t n_basis,
+                   const double *mus, double gamma, const double *W, const double *r_nk,
+                   int64_t n_pairs, const int64_t *pair_ptr, const int32_t *pair_cell,
+                   const int32_t *pair_region, const double *x, double *pred, int32_t device);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MELISSA_B200_H */

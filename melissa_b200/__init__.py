@@ -1,0 +1,17 @@
+"""melissa_b200: B200-native variational-Bayes hot path of Melissa.
+
+Public surface mirrors the reference's R functions for this path:
+`melissa` / `melissa_vb` (R/melissa_vb.R:86), `create_rbf_object`
+(BPRMeth), `impute_test_met`, `eval_imputation_performance`,
+`eval_cluster_performance` (R/utils.R).  The arithmetic runs in
+libmelissa_b200.so (CUDA, sm_100a); there is no CPU fallback.
+"""
+from .data import MelissaData, create_rbf_object, from_dict, from_nested, to_nested
+from .engine import Engine
+from .evaluate import (cluster_ari, eval_cluster_performance, eval_imputation_performance,
+                       impute_test_met)
+from .vb import MelissaResult, finalize, melissa, melissa_inner, melissa_vb, shard_bounds, vb_loop
+
+__all__ = ["MelissaData", "create_rbf_object", "from_dict", "from_nested", "to_nested", "Engine",
+           "cluster_ari", "eval_cluster_performance", "eval_imputation_performance", "impute_test_met",
+           "MelissaResult", "finalize", "melissa", "melissa_inner", "melissa_vb", "shard_bounds", "vb_loop"]

@@ -1,0 +1,1080 @@
+// melissa_b200: CUDA (sm_100a) implementation of Melissa's mean-field VB loop
+// behind the C ABI declared in include/melissa_b200.h.
+//
+// Reference algorithm: andreaskapou/Melissa R/melissa_vb.R:232-529
+// (melissa_inner).  Nothing here is translated R: the loop is re-cut into a
+// per-CpG sweep, a per-cell soft-max, a region-major contraction and a batched
+// D x D solve, see DESIGN.md.
+//
+// Per-pair record ("stats"), R = D + T doubles, T = D(D+1)/2:
+//     [ g = H^T E[z]  (D) | packed upper triangle of H^T H  (T) ]
+// Per-(region, cluster) record ("U"), same length:
+//     [ m = E[w]      (D) | -1/2 * (m m^T + S) packed, off-diagonals doubled (T) ]
+// so that   U[m,k] . stats[p]  =  m^T H^T E[z] - 1/2 tr(H^T H (m m^T + S))
+// is the pair's E-step term (R/melissa_vb.R:325-326), and
+//     acc[m,k] = sum_n r_nk * stats[p]
+// is everything the M-step needs from the data (:368-373).
+#include "melissa_b200.h"
+#include "special.cuh"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <string>
+#include <vector>
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char *fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CU(call)                                                                          \
+    do {                                                                                  \
+        cudaError_t e_ = (call);                                                          \
+        if (e_ != cudaSuccess)                                                            \
+            return fail(MELISSA_ERR_CUDA, "%s:%d: %s failed: %s", __FILE__, __LINE__, #call, \
+                        cudaGetErrorString(e_));                                          \
+    } while (0)
+
+constexpr int MAX_D = 8;        // basis$M <= 7 (the reference's experiments use M = 3, 4, 7)
+constexpr int MAX_MUS = 15;
+
+struct BasisDev {
+    int D;
+    double gamma;
+    double mus[MAX_MUS];
+};
+
+// Small per-fit scalar block in device memory, all length-K arrays.
+struct Scalars {
+    double *beta, *delta0, *delta, *elogpi, *Eww, *Eww_acc, *pi, *logdet_acc, *lb_out;
+};
+
+}  // namespace
+
+struct melissa_handle {
+    int device = 0;
+    int N = 0, M = 0, D = 0, T = 0, R = 0;
+    int64_t P = 0, nnz = 0;
+    BasisDev basis{};
+    // packed observations (device)
+    int64_t *pair_ptr = nullptr;
+    int32_t *pair_cell = nullptr, *pair_region = nullptr;
+    double *x = nullptr;
+    uint8_t *y = nullptr;
+    int64_t *reg_ptr = nullptr;
+    int32_t *reg_pair = nullptr, *reg_cell = nullptr;
+    double *stats = nullptr;       // [P][R]
+    // VB state (device)
+    int K = 0;
+    int64_t N_total = 0;
+    double alpha_0 = 0, beta_0 = 0, alpha_k = 0;
+    double *U = nullptr;           // [M][K][R]
+    double *Spk = nullptr;         // [M][K][T]
+    double *r = nullptr, *log_r = nullptr, *log_rho = nullptr;   // [N][K]
+    double *red = nullptr;         // [M*K*R | K colsum | 1 sum r log r]
+    int64_t red_len = 0;
+    double *lbbuf = nullptr;       // [lb_pz_qz partial | #CpG with s*mu < -5]
+    double *scal_mem = nullptr;
+    Scalars sc{};
+    cudaStream_t stream = nullptr;
+    int64_t launches = 0;
+    bool begun = false;
+    int sm_count = 148;
+};
+
+namespace {
+
+using namespace melissa;
+
+__host__ __device__ inline int tri_index(int D, int i, int j) {   // i <= j, row-major upper triangle
+    return i * D - (i * (i - 1)) / 2 + (j - i);
+}
+
+template <int D>
+__device__ __forceinline__ void eval_basis(double x, const BasisDev &b, double (&h)[D]) {
+    h[0] = 1.0;
+#pragma unroll
+    for (int j = 1; j < D; ++j) {
+        const double d = x - b.mus[j - 1];
+        h[j] = exp(-b.gamma * d * d);
+    }
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Block-wide sum, result valid in thread 0.  blockDim.x multiple of 32, <= 1024.
+__device__ inline double block_sum(double v, double *smem32) {
+    v = warp_sum(v);
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    __syncthreads();
+    if (lane == 0) smem32[w] = v;
+    __syncthreads();
+    if (w == 0) {
+        v = (lane < (int)(blockDim.x >> 5)) ? smem32[lane] : 0.0;
+        v = warp_sum(v);
+    }
+    return v;
+}
+
+// ---------------------------------------------------------------------------
+// H^T H per pair, once at pack time (R/melissa_vb.R:254-255).
+// ---------------------------------------------------------------------------
+template <int D>
+__global__ void __launch_bounds__(128) hh_kernel(const int64_t *__restrict__ pair_ptr,
+                                                 const double *__restrict__ x, double *__restrict__ stats,
+                                                 int64_t P, BasisDev basis) {
+    constexpr int T = D * (D + 1) / 2, R = D + T;
+    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P;
+         p += (int64_t)gridDim.x * blockDim.x) {
+        double hh[T];
+#pragma unroll
+        for (int t = 0; t < T; ++t) hh[t] = 0.0;
+        const int64_t b = pair_ptr[p], e = pair_ptr[p + 1];
+        for (int64_t i = b; i < e; ++i) {
+            double h[D];
+            eval_basis<D>(x[i], basis, h);
+            int t = 0;
+#pragma unroll
+            for (int a = 0; a < D; ++a)
+#pragma unroll
+                for (int c = a; c < D; ++c) hh[t++] += h[a] * h[c];
+        }
+        double *rec = stats + p * R;
+#pragma unroll
+        for (int d = 0; d < D; ++d) rec[d] = 0.0;
+#pragma unroll
+        for (int t = 0; t < T; ++t) rec[D + t] = hh[t];
+    }
+}
+
+// ---------------------------------------------------------------------------
+// The per-CpG sweep (R/melissa_vb.R:418-435 refresh, fused with the NEXT
+// iteration's E-step terms :322-327 and, when WITH_LB, lb_pz_qz :469-473).
+// v1: one thread per pair.
+// ---------------------------------------------------------------------------
+template <int D, bool WITH_LB, bool UNIFORM_R>
+__global__ void __launch_bounds__(128)
+sweep_kernel(const int64_t *__restrict__ pair_ptr, const int32_t *__restrict__ pair_cell,
+             const int32_t *__restrict__ pair_region, const double *__restrict__ x,
+             const uint8_t *__restrict__ y, double *__restrict__ stats, const double *__restrict__ U,
+             const double *__restrict__ r, double *__restrict__ log_rho, double *__restrict__ lbbuf,
+             int64_t P, int K, BasisDev basis) {
+    constexpr int T = D * (D + 1) / 2, R = D + T;
+    __shared__ double red_smem[32];
+    double lb_local = 0.0, wrong_side = 0.0;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t P_round = (P + 31) & ~int64_t(31);
+    const double inv_K = 1.0 / (double)K;
+    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P_round; p += stride) {
+        const bool valid = p < P;
+        int n = -1, m = 0;
+        double g[D];
+#pragma unroll
+        for (int d = 0; d < D; ++d) g[d] = 0.0;
+        const double *Um = U;
+        if (valid) {
+            n = pair_cell[p];
+            m = pair_region[p];
+            Um = U + (int64_t)m * K * R;
+            double wbar[D];
+#pragma unroll
+            for (int d = 0; d < D; ++d) wbar[d] = 0.0;
+            for (int k = 0; k < K; ++k) {
+                const double rk = UNIFORM_R ? 1.0 : r[(int64_t)n * K + k];
+#pragma unroll
+                for (int d = 0; d < D; ++d) wbar[d] += rk * Um[k * R + d];
+            }
+            if (UNIFORM_R) {
+#pragma unroll
+                for (int d = 0; d < D; ++d) wbar[d] *= inv_K;      // rowMeans, R/melissa_vb.R:291
+            }
+            const int64_t b = pair_ptr[p], e = pair_ptr[p + 1];
+            for (int64_t i = b; i < e; ++i) {
+                double h[D];
+                eval_basis<D>(x[i], basis, h);
+                double mu = wbar[0];
+#pragma unroll
+                for (int d = 1; d < D; ++d) mu += h[d] * wbar[d];
+                const bool yi = y[i] != 0;
+                const double t = yi ? mu : -mu;
+                const double G = trunc_mean(t);
+                const double Ez = yi ? G : -G;
+                g[0] += Ez;
+#pragma unroll
+                for (int d = 1; d < D; ++d) g[d] += h[d] * Ez;
+                if (WITH_LB) {
+                    lb_local += 0.5 * mu * mu + loglik_term(mu, yi);
+                    if (t < -5.0) wrong_side += 1.0;
+                }
+            }
+            double *rec = stats + p * R;
+#pragma unroll
+            for (int d = 0; d < D; ++d) rec[d] = g[d];
+        }
+        // E-step terms of the next iteration, reduced per cell.
+        const unsigned full = 0xffffffffu;
+        const int n0 = __shfl_sync(full, n, 0);
+        const bool uniform = __all_sync(full, n == n0 || !valid);
+        double hh[T];
+        if (valid) {
+            const double *rec = stats + p * R + D;
+#pragma unroll
+            for (int t = 0; t < T; ++t) hh[t] = rec[t];
+        } else {
+#pragma unroll
+            for (int t = 0; t < T; ++t) hh[t] = 0.0;
+        }
+        for (int k = 0; k < K; ++k) {
+            double lin = 0.0, trc = 0.0;
+            if (valid) {
+                const double *u = Um + k * R;
+#pragma unroll
+                for (int d = 0; d < D; ++d) lin += u[d] * g[d];
+#pragma unroll
+                for (int t = 0; t < T; ++t) trc += u[D + t] * hh[t];
+                if (WITH_LB) lb_local += (UNIFORM_R ? inv_K : r[(int64_t)n * K + k]) * trc;
+            }
+            double v = lin + trc;
+            if (uniform) {
+                v = warp_sum(v);
+                if ((threadIdx.x & 31) == 0 && n0 >= 0) atomicAdd(&log_rho[(int64_t)n0 * K + k], v);
+            } else if (valid) {
+                atomicAdd(&log_rho[(int64_t)n * K + k], v);
+            }
+        }
+    }
+    if (WITH_LB) {
+        double s = block_sum(lb_local, red_smem);
+        if (threadIdx.x == 0) atomicAdd(&lbbuf[0], s);
+        s = block_sum(wrong_side, red_smem);
+        if (threadIdx.x == 0 && s != 0.0) atomicAdd(&lbbuf[1], s);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// Responsibilities (R/melissa_vb.R:330-331) + colSums(r) (:336) + sum r log r (:482).
+// One thread per cell.  Clears log_rho for the next sweep and the E_ww / logdet
+// accumulators for the solve that follows.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+resp_kernel(double *__restrict__ log_rho, const double *__restrict__ elogpi, double *__restrict__ r,
+            double *__restrict__ log_r, double *__restrict__ colsum, double *__restrict__ rlogr,
+            double *__restrict__ Eww_acc, double *__restrict__ logdet_acc, int N, int K) {
+    __shared__ double red_smem[32];
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (blockIdx.x == 0 && threadIdx.x < K) Eww_acc[threadIdx.x] = 0.0;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        *logdet_acc = 0.0;
+        for (int k = blockDim.x; k < K; ++k) Eww_acc[k] = 0.0;
+    }
+    double lse = 0.0, rl = 0.0;
+    if (n < N) {
+        double mx = -INFINITY;
+        for (int k = 0; k < K; ++k) mx = fmax(mx, log_rho[(int64_t)n * K + k] + elogpi[k]);
+        double s = 0.0;
+        for (int k = 0; k < K; ++k) s += exp(log_rho[(int64_t)n * K + k] + elogpi[k] - mx);
+        lse = log(s) + mx;                                     // R/utils.R:16-20
+    }
+    for (int k = 0; k < K; ++k) {
+        double rk = 0.0;
+        if (n < N) {
+            const double lr = log_rho[(int64_t)n * K + k] + elogpi[k] - lse;
+            rk = exp(lr);
+            log_r[(int64_t)n * K + k] = lr;
+            r[(int64_t)n * K + k] = rk;
+            log_rho[(int64_t)n * K + k] = 0.0;
+            rl += rk * lr;
+        }
+        const double s = block_sum(rk, red_smem);
+        if (threadIdx.x == 0) atomicAdd(&colsum[k], s);
+    }
+    const double s = block_sum(rl, red_smem);
+    if (threadIdx.x == 0) atomicAdd(rlogr, s);
+}
+
+// ---------------------------------------------------------------------------
+// Region-major contraction  acc[m,k,:] = sum_{pairs of region m} r[n,k] * stats[p,:]
+// (the [K x N] x [N x M(D^2+D)] product of R/melissa_vb.R:368-373).
+// v1: one warp per slice of a region's pair list; lane j owns record component(s) j, j+32, ...
+// ---------------------------------------------------------------------------
+template <int J, int KC>
+__global__ void __launch_bounds__(128)
+contract_kernel(const int64_t *__restrict__ reg_ptr, const int32_t *__restrict__ reg_pair,
+                const int32_t *__restrict__ reg_cell, const double *__restrict__ stats,
+                const double *__restrict__ r, double *__restrict__ acc_out, int K, int R) {
+    const int m = blockIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int slice = blockIdx.y * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int nslice = gridDim.y * (blockDim.x >> 5);
+    const int64_t q0 = reg_ptr[m], L = reg_ptr[m + 1] - q0;
+    const int64_t qb = q0 + (L * slice) / nslice, qe = q0 + (L * (slice + 1)) / nslice;
+    if (qb >= qe) return;
+    for (int k0 = 0; k0 < K; k0 += KC) {
+        double acc[J][KC];
+#pragma unroll
+        for (int j = 0; j < J; ++j)
+#pragma unroll
+            for (int c = 0; c < KC; ++c) acc[j][c] = 0.0;
+        for (int64_t base = qb; base < qe; base += 32) {
+            const int64_t q = base + lane;
+            const int32_t my_p = q < qe ? reg_pair[q] : 0;
+            const int32_t my_n = q < qe ? reg_cell[q] : 0;
+            const int cnt = (int)min((int64_t)32, qe - base);
+#pragma unroll 4
+            for (int it = 0; it < cnt; ++it) {
+                const int64_t p = __shfl_sync(0xffffffffu, my_p, it);
+                const int64_t n = __shfl_sync(0xffffffffu, my_n, it);
+                double rk[KC];
+#pragma unroll
+                for (int c = 0; c < KC; ++c) rk[c] = (k0 + c < K) ? r[n * K + k0 + c] : 0.0;
+#pragma unroll
+                for (int j = 0; j < J; ++j) {
+                    const int idx = lane + 32 * j;
+                    const double s = idx < R ? stats[p * R + idx] : 0.0;
+#pragma unroll
+                    for (int c = 0; c < KC; ++c) acc[j][c] += rk[c] * s;
+                }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < J; ++j) {
+            const int idx = lane + 32 * j;
+            if (idx < R) {
+#pragma unroll
+                for (int c = 0; c < KC; ++c)
+                    if (k0 + c < K) atomicAdd(&acc_out[((int64_t)m * K + k0 + c) * R + idx], acc[j][c]);
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// q(w_mk): S = ((alpha/beta_k + 1e-7) I + sum r HH)^-1, m = S sum r H^T E[z]
+// (R/melissa_vb.R:368-375), by Cholesky.  One thread per (region, cluster).
+// ---------------------------------------------------------------------------
+template <int D>
+__global__ void __launch_bounds__(128)
+solve_kernel(const double *__restrict__ acc, double *__restrict__ U, double *__restrict__ Spk,
+             const double *__restrict__ beta, double *__restrict__ Eww_acc,
+             double *__restrict__ logdet_acc, int M, int K, double alpha_k) {
+    constexpr int T = D * (D + 1) / 2, R = D + T;
+    __shared__ double red_smem[32];
+    const int m = blockIdx.x * blockDim.x + threadIdx.x;
+    const int k = blockIdx.y;
+    double eww = 0.0, logdetS = 0.0;
+    if (m < M) {
+        const double *rec = acc + ((int64_t)m * K + k) * R;
+        const double ridge = alpha_k / beta[k] + 1e-7;
+        double A[D][D];      // lower triangle used
+        double b[D];
+#pragma unroll
+        for (int i = 0; i < D; ++i) b[i] = rec[i];
+        {
+            int t = 0;
+#pragma unroll
+            for (int i = 0; i < D; ++i)
+#pragma unroll
+                for (int j = i; j < D; ++j) {
+                    A[j][i] = rec[D + t] + (i == j ? ridge : 0.0);
+                    ++t;
+                }
+        }
+        // Cholesky A = L L^T, in place (lower).
+#pragma unroll
+        for (int j = 0; j < D; ++j) {
+            double d = A[j][j];
+#pragma unroll
+            for (int c = 0; c < j; ++c) d -= A[j][c] * A[j][c];
+            const double ljj = sqrt(d);
+            A[j][j] = ljj;
+            logdetS -= 2.0 * log(ljj);
+            const double inv = 1.0 / ljj;
+#pragma unroll
+            for (int i = j + 1; i < D; ++i) {
+                double s = A[i][j];
+#pragma unroll
+                for (int c = 0; c < j; ++c) s -= A[i][c] * A[j][c];
+                A[i][j] = s * inv;
+            }
+        }
+        // Li = L^-1 (lower), in place.
+#pragma unroll
+        for (int j = 0; j < D; ++j) {
+            A[j][j] = 1.0 / A[j][j];
+#pragma unroll
+            for (int i = j + 1; i < D; ++i) {
+                double s = 0.0;
+#pragma unroll
+                for (int c = j; c < i; ++c) s -= A[i][c] * A[c][j];
+                A[i][j] = s / A[i][i];
+            }
+        }
+        // S = Li^T Li ; mvec = S b.
+        double S[T];
+        {
+            int t = 0;
+#pragma unroll
+            for (int i = 0; i < D; ++i)
+#pragma unroll
+                for (int j = i; j < D; ++j) {
+                    double s = 0.0;
+#pragma unroll
+                    for (int c = j; c < D; ++c) s += A[c][i] * A[c][j];
+                    S[t++] = s;
+                }
+        }
+        double mv[D];
+#pragma unroll
+        for (int i = 0; i < D; ++i) {
+            double s = 0.0;
+#pragma unroll
+            for (int j = 0; j < D; ++j) s += S[i <= j ? tri_index(D, i, j) : tri_index(D, j, i)] * b[j];
+            mv[i] = s;
+        }
+        double *u = U + ((int64_t)m * K + k) * R;
+        double *sp = Spk + ((int64_t)m * K + k) * T;
+        {
+            int t = 0;
+#pragma unroll
+            for (int i = 0; i < D; ++i) {
+                u[i] = mv[i];
+                eww += mv[i] * mv[i] + S[tri_index(D, i, i)];
+#pragma unroll
+                for (int j = i; j < D; ++j) {
+                    const double c = mv[i] * mv[j] + S[t];
+                    u[D + t] = (i == j ? -0.5 : -1.0) * c;
+                    sp[t] = S[t];
+                    ++t;
+                }
+            }
+        }
+    }
+    double s = block_sum(eww, red_smem);
+    if (threadIdx.x == 0) atomicAdd(&Eww_acc[k], s);
+    s = block_sum(logdetS, red_smem);
+    if (threadIdx.x == 0) atomicAdd(logdet_acc, s);
+}
+
+// Initial q(w): m = w0, S = solve(diag(50, D)) (R/melissa_vb.R:266-269, :279-280).
+template <int D>
+__global__ void init_params_kernel(const double *__restrict__ w0, double *__restrict__ U,
+                                   double *__restrict__ Spk, int M, int K) {
+    constexpr int T = D * (D + 1) / 2, R = D + T;
+    const int m = blockIdx.x * blockDim.x + threadIdx.x;
+    const int k = blockIdx.y;
+    if (m >= M) return;
+    double mv[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) mv[d] = w0[m + (int64_t)M * (d + D * k)];
+    double *u = U + ((int64_t)m * K + k) * R;
+    double *sp = Spk + ((int64_t)m * K + k) * T;
+    int t = 0;
+#pragma unroll
+    for (int i = 0; i < D; ++i) {
+        u[i] = mv[i];
+#pragma unroll
+        for (int j = i; j < D; ++j) {
+            const double s = (i == j) ? 1.0 / 50.0 : 0.0;
+            u[D + t] = (i == j ? -0.5 : -1.0) * (mv[i] * mv[j] + s);
+            sp[t] = s;
+            ++t;
+        }
+    }
+}
+
+// beta / delta / pi / E[log pi]  (R/melissa_vb.R:336-338, :386-392, :443).  One thread.
+__global__ void scalars_kernel(Scalars sc, const double *__restrict__ colsum, int K, double alpha_k,
+                               double beta_0, double N_total, int init) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    double sum_delta = 0.0;
+    for (int k = 0; k < K; ++k) {
+        if (init) {
+            sc.beta[k] = beta_0;
+            sc.Eww[k] = 0.0;
+            sc.delta[k] = sc.delta0[k];
+            sc.pi[k] = 0.0;
+        } else {
+            sc.Eww[k] = sc.Eww_acc[k];
+            double b = beta_0 + 0.5 * sc.Eww[k];
+            if (b > 10.0 * alpha_k) b = 10.0 * alpha_k;
+            sc.beta[k] = b;
+            sc.delta[k] = sc.delta0[k] + colsum[k];
+            sc.pi[k] = (sc.delta0[k] + colsum[k]) / (K * sc.delta0[k] + N_total);
+        }
+        sum_delta += sc.delta[k];
+    }
+    const double dsum = digamma_pos(sum_delta);
+    for (int k = 0; k < K; ++k) sc.elogpi[k] = digamma_pos(sc.delta[k]) - dsum;
+}
+
+// Lower bound assembly (R/melissa_vb.R:475-492).  One thread.
+__global__ void lb_kernel(Scalars sc, const double *__restrict__ colsum, const double *__restrict__ rlogr,
+                          const double *__restrict__ lbbuf, int K, int M, int D, double alpha_0,
+                          double alpha_k, double beta_0) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const double LOG2PI = 1.83787706640934548356;
+    const double MD = (double)M * D;
+    const double dga = digamma_pos(alpha_k);
+    double lb_p_w = 0, lb_p_c = 0, lb_p_pi = 0, lb_p_tau = 0, lb_q_pi = 0, lb_q_tau = 0;
+    double sum_d0 = 0, sum_dk = 0, sum_lg0 = 0, sum_lgk = 0;
+    for (int k = 0; k < K; ++k) {
+        const double dg = dga - log(sc.beta[k]);
+        const double E_alpha = alpha_k / sc.beta[k];
+        lb_p_w += -0.5 * MD * LOG2PI + 0.5 * MD * dg - 0.5 * E_alpha * sc.Eww[k];
+        lb_p_c += colsum[k] * sc.elogpi[k];
+        lb_p_pi += (sc.delta0[k] - 1.0) * sc.elogpi[k];
+        lb_q_pi += (sc.delta[k] - 1.0) * sc.elogpi[k];
+        sum_d0 += sc.delta0[k];
+        sum_dk += sc.delta[k];
+        sum_lg0 += lgamma(sc.delta0[k]);
+        sum_lgk += lgamma(sc.delta[k]);
+        lb_p_tau += alpha_0 * log(beta_0) + (alpha_0 - 1.0) * dg - beta_0 * E_alpha - lgamma(alpha_0);
+        lb_q_tau += -lgamma(alpha_k) + (alpha_k - 1.0) * dga + log(sc.beta[k]) - alpha_k;
+    }
+    lb_p_pi += lgamma(sum_d0) - sum_lg0;
+    lb_q_pi += lgamma(sum_dk) - sum_lgk;
+    const double lb_q_w = -0.5 * (*sc.logdet_acc) - 0.5 * D * (1.0 + LOG2PI) * (double)M * K;
+    const double lb_q_c = *rlogr;
+    *sc.lb_out = lbbuf[0] + lb_p_c + lb_p_pi + lb_p_w + lb_p_tau - lb_q_c - lb_q_pi - lb_q_w - lb_q_tau;
+}
+
+// Imputation (R/utils.R:246-265): pred = round(sum_k r_nk Phi(h . W[m,,k]), 3).
+// W and r_nk are in R's column-major layouts (dim c(M, D, K) and c(N, K)).
+template <int D>
+__global__ void impute_kernel(const int64_t *__restrict__ pair_ptr, const int32_t *__restrict__ pair_cell,
+                              const int32_t *__restrict__ pair_region, const double *__restrict__ x,
+                              const double *__restrict__ W, const double *__restrict__ r_nk,
+                              double *__restrict__ pred, int64_t P, int N, int M, int K, BasisDev basis) {
+    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P;
+         p += (int64_t)gridDim.x * blockDim.x) {
+        const int n = pair_cell[p], m = pair_region[p];
+        for (int64_t i = pair_ptr[p]; i < pair_ptr[p + 1]; ++i) {
+            double h[D];
+            eval_basis<D>(x[i], basis, h);
+            double s = 0.0;
+            for (int k = 0; k < K; ++k) {
+                const double *w = W + m + (int64_t)M * D * k;
+                double z = w[0];
+#pragma unroll
+                for (int d = 1; d < D; ++d) z += h[d] * w[(int64_t)M * d];
+                s += r_nk[n + (int64_t)N * k] * norm_cdf(z);
+            }
+            pred[i] = rint(s * 1000.0) / 1000.0;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// launch helpers
+// ---------------------------------------------------------------------------
+int grid_for(int64_t work, int block, int sm_count, int per_sm) {
+    const int64_t need = (work + block - 1) / block;
+    return (int)std::max<int64_t>(1, std::min<int64_t>(need, (int64_t)sm_count * per_sm));
+}
+
+#define DISPATCH_D(D_, ...)                                                       \
+    switch (D_) {                                                                 \
+        case 1: { constexpr int DD = 1; __VA_ARGS__; } break;                     \
+        case 2: { constexpr int DD = 2; __VA_ARGS__; } break;                     \
+        case 3: { constexpr int DD = 3; __VA_ARGS__; } break;                     \
+        case 4: { constexpr int DD = 4; __VA_ARGS__; } break;                     \
+        case 5: { constexpr int DD = 5; __VA_ARGS__; } break;                     \
+        case 6: { constexpr int DD = 6; __VA_ARGS__; } break;                     \
+        case 7: { constexpr int DD = 7; __VA_ARGS__; } break;                     \
+        case 8: { constexpr int DD = 8; __VA_ARGS__; } break;                     \
+        default: return fail(MELISSA_ERR_ARG, "unsupported D = %d", D_);          \
+    }
+
+int launch_sweep(melissa_handle *h, bool with_lb, bool uniform_r) {
+    const int block = 128;
+    const int grid = grid_for(h->P, block, h->sm_count, 16);
+#define SWEEP(LB_, UNI_)                                                                        \
+    DISPATCH_D(h->D, sweep_kernel<DD, LB_, UNI_><<<grid, block, 0, h->stream>>>(                 \
+                         h->pair_ptr, h->pair_cell, h->pair_region, h->x, h->y, h->stats, h->U, \
+                         h->r, h->log_rho, h->lbbuf, h->P, h->K, h->basis))
+    if (with_lb && uniform_r) { SWEEP(true, true) }
+    else if (with_lb) { SWEEP(true, false) }
+    else if (uniform_r) { SWEEP(false, true) }
+    else { SWEEP(false, false) }
+#undef SWEEP
+    h->launches++;
+    CU(cudaGetLastError());
+    return MELISSA_OK;
+}
+
+int launch_contract(melissa_handle *h) {
+    const int J = (h->R + 31) / 32;
+    int slices = (int)std::max<int64_t>(1, std::min<int64_t>(64, ((int64_t)h->sm_count * 32) / std::max(1, h->M)));
+    // each slice should still have a few dozen pairs
+    const int64_t avg = h->P / std::max(1, h->M);
+    while (slices > 1 && avg / slices < 32) slices >>= 1;
+    const dim3 grid(h->M, (slices + 3) / 4);
+    const int block = 128;
+    double *acc = h->red;
+#define CONTRACT(J_, KC_)                                                                     \
+    contract_kernel<J_, KC_><<<grid, block, 0, h->stream>>>(h->reg_ptr, h->reg_pair, h->reg_cell, \
+                                                          h->stats, h->r, acc, h->K, h->R)
+    if (J == 1) {
+        if (h->K <= 4) CONTRACT(1, 4);
+        else if (h->K <= 8) CONTRACT(1, 8);
+        else CONTRACT(1, 16);
+    } else if (J == 2) {
+        if (h->K <= 4) CONTRACT(2, 4);
+        else CONTRACT(2, 8);
+    } else {
+        return fail(MELISSA_ERR_ARG, "record length %d not supported", h->R);
+    }
+#undef CONTRACT
+    h->launches++;
+    CU(cudaGetLastError());
+    return MELISSA_OK;
+}
+
+template <typename Tp>
+int dev_alloc(Tp **p, int64_t n) {
+    *p = nullptr;
+    CU(cudaMalloc((void **)p, std::max<int64_t>(1, n) * sizeof(Tp)));
+    return MELISSA_OK;
+}
+
+void free_fit(melissa_handle *h) {
+    cudaFree(h->U); cudaFree(h->Spk); cudaFree(h->r); cudaFree(h->log_r); cudaFree(h->log_rho);
+    cudaFree(h->red); cudaFree(h->lbbuf); cudaFree(h->scal_mem);
+    h->U = h->Spk = h->r = h->log_r = h->log_rho = h->red = h->lbbuf = h->scal_mem = nullptr;
+    h->begun = false;
+}
+
+}  // namespace
+
+// ===========================================================================
+// C ABI
+// ===========================================================================
+extern "C" {
+
+const char *melissa_last_error(void) { return g_err.c_str(); }
+int melissa_abi_version(void) { return 1; }
+
+int melissa_pack(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const int64_t *pair_ptr,
+                 const int32_t *pair_cell, const int32_t *pair_region, const double *x,
+                 const uint8_t *y, int32_t basis_kind, int32_t n_basis, const double *mus,
+                 double gamma, int32_t device, int32_t allow_empty_regions, melissa_handle **out) {
+    if (!out) return fail(MELISSA_ERR_ARG, "out is NULL");
+    *out = nullptr;
+    if (n_cells <= 0 || n_regions <= 0) return fail(MELISSA_ERR_ARG, "N > 0 and M > 0 are required");
+    if (n_pairs <= 0 || !pair_ptr || !pair_cell || !pair_region || !x || !y)
+        return fail(MELISSA_ERR_ARG, "empty or NULL observation arrays");
+    if (n_pairs >= (int64_t)std::numeric_limits<int32_t>::max())
+        return fail(MELISSA_ERR_ARG, "more than 2^31-1 pairs on one GPU; shard the cells");
+    if (basis_kind != MELISSA_BASIS_RBF)
+        return fail(MELISSA_ERR_ARG, "only the RBF basis object is supported (polynomial / Fourier are not pinned)");
+    if (n_basis < 0 || n_basis + 1 > MAX_D || (n_basis > 0 && !mus))
+        return fail(MELISSA_ERR_ARG, "basis$M must be in 0..%d", MAX_D - 1);
+    if (!(gamma > 0.0) && n_basis > 0) return fail(MELISSA_ERR_ARG, "basis$gamma must be positive");
+    // ---- validate the pair list (host) and build the region-major index
+    const int64_t P = n_pairs;
+    if (pair_ptr[0] != 0) return fail(MELISSA_ERR_ARG, "pair_ptr[0] must be 0");
+    std::vector<int64_t> reg_cnt((size_t)n_regions + 1, 0);
+    int32_t prev_cell = -1, prev_region = -1;
+    int32_t cells_seen = 0;
+    for (int64_t p = 0; p < P; ++p) {
+        const int32_t n = pair_cell[p], m = pair_region[p];
+        if (n < 0 || n >= n_cells || m < 0 || m >= n_regions)
+            return fail(MELISSA_ERR_ARG, "pair %lld: cell/region index out of range", (long long)p);
+        if (n < prev_cell) return fail(MELISSA_ERR_ARG, "pairs must be cell-major (pair %lld)", (long long)p);
+        if (n != prev_cell) {
+            if (n != prev_cell + 1)
+                return fail(MELISSA_ERR_ARG, "cell %d: No coverage across all regions. This cell should be discarded!",
+                            prev_cell + 1);
+            ++cells_seen;
+            prev_region = -1;
+        }
+        if (m <= prev_region)
+            return fail(MELISSA_ERR_ARG, "regions must be strictly increasing inside a cell (pair %lld)", (long long)p);
+        if (pair_ptr[p + 1] <= pair_ptr[p])
+            return fail(MELISSA_ERR_ARG, "pair %lld has no CpG", (long long)p);
+        prev_cell = n;
+        prev_region = m;
+        reg_cnt[(size_t)m + 1]++;
+    }
+    if (cells_seen != n_cells)
+        return fail(MELISSA_ERR_ARG, "cell %d: No coverage across all regions. This cell should be discarded!", cells_seen);
+    const int64_t nnz = pair_ptr[P];
+    for (int64_t i = 0; i < nnz; ++i)
+        if (y[i] > 1) return fail(MELISSA_ERR_ARG, "methylation state y[%lld] is not 0/1", (long long)i);
+    if (!allow_empty_regions)
+        for (int32_t m = 0; m < n_regions; ++m)
+            if (reg_cnt[(size_t)m + 1] == 0)
+                return fail(MELISSA_ERR_ARG, "region %d is not covered by any cell", m);
+    for (int32_t m = 0; m < n_regions; ++m) reg_cnt[(size_t)m + 1] += reg_cnt[m];
+    std::vector<int32_t> reg_pair((size_t)P), reg_cell((size_t)P);
+    {
+        std::vector<int64_t> cursor(reg_cnt.begin(), reg_cnt.end() - 1);
+        for (int64_t p = 0; p < P; ++p) {
+            const int64_t q = cursor[pair_region[p]]++;
+            reg_pair[(size_t)q] = (int32_t)p;
+            reg_cell[(size_t)q] = pair_cell[p];
+        }
+    }
+    // ---- device side
+    CU(cudaSetDevice(device));
+    melissa_handle *h = new melissa_handle();
+    h->device = device;
+    h->N = n_cells; h->M = n_regions; h->P = P; h->nnz = nnz;
+    h->D = n_basis + 1; h->T = h->D * (h->D + 1) / 2; h->R = h->D + h->T;
+    h->basis.D = h->D; h->basis.gamma = gamma;
+    for (int j = 0; j < MAX_MUS; ++j) h->basis.mus[j] = j < n_basis ? mus[j] : 0.0;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) h->sm_count = prop.multiProcessorCount;
+    int rc = MELISSA_OK;
+    auto bail = [&](int code) { melissa_free(h); return code; };
+    if ((rc = dev_alloc(&h->pair_ptr, P + 1))) return bail(rc);
+    if ((rc = dev_alloc(&h->pair_cell, P))) return bail(rc);
+    if ((rc = dev_alloc(&h->pair_region, P))) return bail(rc);
+    if ((rc = dev_alloc(&h->x, nnz))) return bail(rc);
+    if ((rc = dev_alloc(&h->y, nnz))) return bail(rc);
+    if ((rc = dev_alloc(&h->reg_ptr, (int64_t)n_regions + 1))) return bail(rc);
+    if ((rc = dev_alloc(&h->reg_pair, P))) return bail(rc);
+    if ((rc = dev_alloc(&h->reg_cell, P))) return bail(rc);
+    if ((rc = dev_alloc(&h->stats, P * h->R))) return bail(rc);
+#define H2D(dst, src, n, Tp)                                                                          \
+    if (cudaMemcpyAsync(dst, src, (size_t)(n) * sizeof(Tp), cudaMemcpyHostToDevice, nullptr) != cudaSuccess) \
+        return bail(fail(MELISSA_ERR_CUDA, "H2D copy of " #src " failed: %s", cudaGetErrorString(cudaGetLastError())))
+    H2D(h->pair_ptr, pair_ptr, P + 1, int64_t);
+    H2D(h->pair_cell, pair_cell, P, int32_t);
+    H2D(h->pair_region, pair_region, P, int32_t);
+    H2D(h->x, x, nnz, double);
+    H2D(h->y, y, nnz, uint8_t);
+    H2D(h->reg_ptr, reg_cnt.data(), n_regions + 1, int64_t);
+    H2D(h->reg_pair, reg_pair.data(), P, int32_t);
+    H2D(h->reg_cell, reg_cell.data(), P, int32_t);
+#undef H2D
+    {
+        const int grid = grid_for(P, 128, h->sm_count, 16);
+        auto run = [&]() -> int {
+            DISPATCH_D(h->D, hh_kernel<DD><<<grid, 128>>>(h->pair_ptr, h->x, h->stats, P, h->basis));
+            return MELISSA_OK;
+        };
+        if ((rc = run())) return bail(rc);
+        h->launches++;
+    }
+    if (cudaDeviceSynchronize() != cudaSuccess)
+        return bail(fail(MELISSA_ERR_CUDA, "pack failed: %s", cudaGetErrorString(cudaGetLastError())));
+    *out = h;
+    return MELISSA_OK;
+}
+
+int melissa_free(melissa_handle *h) {
+    if (!h) return MELISSA_OK;
+    cudaSetDevice(h->device);
+    free_fit(h);
+    cudaFree(h->pair_ptr); cudaFree(h->pair_cell); cudaFree(h->pair_region); cudaFree(h->x);
+    cudaFree(h->y); cudaFree(h->reg_ptr); cudaFree(h->reg_pair); cudaFree(h->reg_cell);
+    cudaFree(h->stats);
+    delete h;
+    return MELISSA_OK;
+}
+
+int melissa_vb_begin(melissa_handle *h, int32_t K, const double *w0, const double *delta_0,
+                     double alpha_0, double beta_0, int64_t n_cells_total, void *stream) {
+    if (!h) return fail(MELISSA_ERR_ARG, "handle is NULL");
+    if (K <= 0 || K > 64) return fail(MELISSA_ERR_ARG, "K must be in 1..64");
+    if (!w0 || !delta_0) return fail(MELISSA_ERR_ARG, "w0 / delta_0 is NULL");
+    if (n_cells_total < h->N) return fail(MELISSA_ERR_ARG, "n_cells_total < cells in this shard");
+    for (int k = 0; k < K; ++k)
+        if (!(delta_0[k] > 0.0)) return fail(MELISSA_ERR_ARG, "delta_0 must be positive");
+    CU(cudaSetDevice(h->device));
+    free_fit(h);
+    h->K = K;
+    h->stream = (cudaStream_t)stream;
+    h->N_total = n_cells_total;
+    h->alpha_0 = alpha_0;
+    h->alpha_k = alpha_0 + (double)h->M * h->D / 2.0;                       // R/melissa_vb.R:264
+    h->beta_0 = std::isnan(beta_0) ? std::sqrt(h->alpha_k) : beta_0;        // :271-273
+    if (!(h->beta_0 > 0.0) || !(alpha_0 > 0.0)) return fail(MELISSA_ERR_ARG, "alpha_0 and beta_0 must be positive");
+    const int64_t MK = (int64_t)h->M * K;
+    int rc;
+    if ((rc = dev_alloc(&h->U, MK * h->R))) return rc;
+    if ((rc = dev_alloc(&h->Spk, MK * h->T))) return rc;
+    if ((rc = dev_alloc(&h->r, (int64_t)h->N * K))) return rc;
+    if ((rc = dev_alloc(&h->log_r, (int64_t)h->N * K))) return rc;
+    if ((rc = dev_alloc(&h->log_rho, (int64_t)h->N * K))) return rc;
+    h->red_len = MK * h->R + K + 1;
+    if ((rc = dev_alloc(&h->red, h->red_len))) return rc;
+    if ((rc = dev_alloc(&h->lbbuf, 2))) return rc;
+    if ((rc = dev_alloc(&h->scal_mem, (int64_t)7 * K + 2))) return rc;
+    double *s = h->scal_mem;
+    h->sc.beta = s; h->sc.delta0 = s + K; h->sc.delta = s + 2 * K; h->sc.elogpi = s + 3 * K;
+    h->sc.Eww = s + 4 * K; h->sc.Eww_acc = s + 5 * K; h->sc.pi = s + 6 * K;
+    h->sc.logdet_acc = s + 7 * K; h->sc.lb_out = s + 7 * K + 1;
+    cudaStream_t st = h->stream;
+    CU(cudaMemsetAsync(h->scal_mem, 0, ((size_t)7 * K + 2) * sizeof(double), st));
+    CU(cudaMemsetAsync(h->log_rho, 0, (size_t)h->N * K * sizeof(double), st));
+    CU(cudaMemsetAsync(h->r, 0, (size_t)h->N * K * sizeof(double), st));
+    CU(cudaMemsetAsync(h->log_r, 0, (size_t)h->N * K * sizeof(double), st));
+    CU(cudaMemsetAsync(h->red, 0, (size_t)h->red_len * sizeof(double), st));
+    CU(cudaMemsetAsync(h->lbbuf, 0, 2 * sizeof(double), st));
+    CU(cudaMemcpyAsync(h->sc.delta0, delta_0, (size_t)K * sizeof(double), cudaMemcpyHostToDevice, st));
+    // stage w0 through the reduction buffer's tail-free head (M*D*K <= M*K*R doubles)
+    CU(cudaMemcpyAsync(h->red, w0, (size_t)MK * h->D * sizeof(double), cudaMemcpyHostToDevice, st));
+    {
+        const dim3 grid((h->M + 127) / 128, K);
+        auto run = [&]() -> int {
+            DISPATCH_D(h->D, init_params_kernel<DD><<<grid, 128, 0, st>>>(h->red, h->U, h->Spk, h->M, K));
+            return MELISSA_OK;
+        };
+        if ((rc = run())) return rc;
+        h->launches++;
+    }
+    CU(cudaMemsetAsync(h->red, 0, (size_t)h->red_len * sizeof(double), st));
+    scalars_kernel<<<1, 32, 0, st>>>(h->sc, h->red + MK * h->R, K, h->alpha_k, h->beta_0, (double)h->N_total, 1);
+    h->launches++;
+    CU(cudaGetLastError());
+    h->begun = true;
+    // mu from rowMeans(w), E[z], E-step terms for i = 2  (R/melissa_vb.R:283-302)
+    return launch_sweep(h, false, true);
+}
+
+int melissa_vb_phase_a(melissa_handle *h) {
+    if (!h || !h->begun) return fail(MELISSA_ERR_STATE, "melissa_vb_begin has not been called");
+    CU(cudaSetDevice(h->device));
+    const int64_t MK = (int64_t)h->M * h->K;
+    CU(cudaMemsetAsync(h->red, 0, (size_t)h->red_len * sizeof(double), h->stream));
+    double *colsum = h->red + MK * h->R, *rlogr = colsum + h->K;
+    resp_kernel<<<(h->N + 127) / 128, 128, 0, h->stream>>>(h->log_rho, h->sc.elogpi, h->r, h->log_r, colsum,
+                                                          rlogr, h->sc.Eww_acc, h->sc.logdet_acc, h->N, h->K);
+    h->launches++;
+    CU(cudaGetLastError());
+    return launch_contract(h);
+}
+
+int melissa_vb_phase_b(melissa_handle *h, int32_t with_lb) {
+    if (!h || !h->begun) return fail(MELISSA_ERR_STATE, "melissa_vb_begin has not been called");
+    CU(cudaSetDevice(h->device));
+    const int64_t MK = (int64_t)h->M * h->K;
+    double *colsum = h->red + MK * h->R;
+    {
+        const dim3 grid((h->M + 127) / 128, h->K);
+        auto run = [&]() -> int {
+            DISPATCH_D(h->D, solve_kernel<DD><<<grid, 128, 0, h->stream>>>(
+                                 h->red, h->U, h->Spk, h->sc.beta, h->sc.Eww_acc, h->sc.logdet_acc, h->M, h->K,
+                                 h->alpha_k));
+            return MELISSA_OK;
+        };
+        int rc;
+        if ((rc = run())) return rc;
+        h->launches++;
+    }
+    scalars_kernel<<<1, 32, 0, h->stream>>>(h->sc, colsum, h->K, h->alpha_k, h->beta_0, (double)h->N_total, 0);
+    h->launches++;
+    CU(cudaGetLastError());
+    if (with_lb) CU(cudaMemsetAsync(h->lbbuf, 0, 2 * sizeof(double), h->stream));
+    return launch_sweep(h, with_lb != 0, false);
+}
+
+int melissa_vb_lower_bound(melissa_handle *h, double *lb_out) {
+    if (!h || !h->begun) return fail(MELISSA_ERR_STATE, "melissa_vb_begin has not been called");
+    CU(cudaSetDevice(h->device));
+    const int64_t MK = (int64_t)h->M * h->K;
+    double *colsum = h->red + MK * h->R, *rlogr = colsum + h->K;
+    lb_kernel<<<1, 32, 0, h->stream>>>(h->sc, colsum, rlogr, h->lbbuf, h->K, h->M, h->D, h->alpha_0, h->alpha_k,
+                                       h->beta_0);
+    h->launches++;
+    CU(cudaGetLastError());
+    double v = 0.0;
+    CU(cudaMemcpyAsync(&v, h->sc.lb_out, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    if (lb_out) *lb_out = v;
+    return MELISSA_OK;
+}
+
+int melissa_vb_reduce_buffer(melissa_handle *h, void **dev_ptr, int64_t *n_doubles) {
+    if (!h || !h->begun) return fail(MELISSA_ERR_STATE, "melissa_vb_begin has not been called");
+    if (dev_ptr) *dev_ptr = h->red;
+    if (n_doubles) *n_doubles = h->red_len;
+    return MELISSA_OK;
+}
+
+int melissa_vb_lb_buffer(melissa_handle *h, void **dev_ptr, int64_t *n_doubles) {
+    if (!h || !h->begun) return fail(MELISSA_ERR_STATE, "melissa_vb_begin has not been called");
+    if (dev_ptr) *dev_ptr = h->lbbuf;
+    if (n_doubles) *n_doubles = 2;
+    return MELISSA_OK;
+}
+
+int melissa_sync(melissa_handle *h) {
+    if (!h) return fail(MELISSA_ERR_ARG, "handle is NULL");
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->stream));
+    return MELISSA_OK;
+}
+
+int64_t melissa_launch_count(const melissa_handle *h) { return h ? h->launches : 0; }
+
+int melissa_vb_fetch(melissa_handle *h, double *W, double *W_Sigma, double *r_nk, double *delta,
+                     double *alpha, double *beta, double *pi_k) {
+    if (!h || !h->begun) return fail(MELISSA_ERR_STATE, "melissa_vb_begin has not been called");
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->stream));
+    const int K = h->K, M = h->M, D = h->D, T = h->T, R = h->R, N = h->N;
+    const int64_t MK = (int64_t)M * K;
+    if (W) {
+        std::vector<double> U((size_t)MK * R);
+        CU(cudaMemcpy(U.data(), h->U, U.size() * sizeof(double), cudaMemcpyDeviceToHost));
+        for (int m = 0; m < M; ++m)
+            for (int k = 0; k < K; ++k)
+                for (int d = 0; d < D; ++d)
+                    W[m + (int64_t)M * (d + (int64_t)D * k)] = U[((size_t)m * K + k) * R + d];
+    }
+    if (W_Sigma) {
+        std::vector<double> S((size_t)MK * T);
+        CU(cudaMemcpy(S.data(), h->Spk, S.size() * sizeof(double), cudaMemcpyDeviceToHost));
+        for (int k = 0; k < K; ++k)
+            for (int m = 0; m < M; ++m) {
+                double *blk = W_Sigma + ((int64_t)k * M + m) * D * D;
+                const double *sp = S.data() + ((size_t)m * K + k) * T;
+                for (int i = 0; i < D; ++i)
+                    for (int j = i; j < D; ++j) {
+                        const double v = sp[tri_index(D, i, j)];
+                        blk[i + D * j] = v;
+                        blk[j + D * i] = v;
+                    }
+            }
+    }
+    if (r_nk) {
+        std::vector<double> r((size_t)N * K);
+        CU(cudaMemcpy(r.data(), h->r, r.size() * sizeof(double), cudaMemcpyDeviceToHost));
+        for (int n = 0; n < N; ++n)
+            for (int k = 0; k < K; ++k) r_nk[n + (int64_t)N * k] = r[(size_t)n * K + k];
+    }
+    if (delta) CU(cudaMemcpy(delta, h->sc.delta, K * sizeof(double), cudaMemcpyDeviceToHost));
+    if (beta) CU(cudaMemcpy(beta, h->sc.beta, K * sizeof(double), cudaMemcpyDeviceToHost));
+    if (pi_k) CU(cudaMemcpy(pi_k, h->sc.pi, K * sizeof(double), cudaMemcpyDeviceToHost));
+    if (alpha)
+        for (int k = 0; k < K; ++k) alpha[k] = h->alpha_k;
+    return MELISSA_OK;
+}
+
+int melissa_vb_fetch_HtEz(melissa_handle *h, double *out) {
+    if (!h || !h->begun) return fail(MELISSA_ERR_STATE, "melissa_vb_begin has not been called");
+    if (!out) return fail(MELISSA_ERR_ARG, "out is NULL");
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->stream));
+    CU(cudaMemcpy2D(out, (size_t)h->D * sizeof(double), h->stats, (size_t)h->R * sizeof(double),
+                    (size_t)h->D * sizeof(double), (size_t)h->P, cudaMemcpyDeviceToHost));
+    return MELISSA_OK;
+}
+
+int melissa_vb_run(melissa_handle *h, int32_t K, const double *w0, const double *delta_0,
+                   double alpha_0, double beta_0, int32_t vb_max_iter, double epsilon_conv,
+                   int32_t lb_every, double *W, double *W_Sigma, double *r_nk, double *delta,
+                   double *alpha, double *beta, double *pi_k, double *lb, int32_t lb_cap,
+                   int32_t *n_lb, int32_t *n_iter, int32_t *flags) {
+    if (!h) return fail(MELISSA_ERR_ARG, "handle is NULL");
+    if (vb_max_iter < 2) return fail(MELISSA_ERR_ARG, "vb_max_iter must be >= 2");
+    if (lb_every <= 0) return fail(MELISSA_ERR_ARG, "lb_every must be positive");
+    int rc;
+    if ((rc = melissa_vb_begin(h, K, w0, delta_0, alpha_0, beta_0, h->N, nullptr))) return rc;
+    double lb_prev = -std::numeric_limits<double>::infinity();              // LB <- c(-Inf), :242
+    int nlb = 0, fl = 0, it = 1;
+    if (lb && lb_cap > 0) lb[0] = lb_prev;
+    nlb = 1;
+    for (int i = 2; i <= vb_max_iter; ++i) {                                // :309
+        it = i;
+        if ((rc = melissa_vb_phase_a(h))) return rc;
+        const bool with_lb = (i % lb_every == 0) || i == vb_max_iter;       // :458
+        if ((rc = melissa_vb_phase_b(h, with_lb))) return rc;
+        if (with_lb) {
+            double v;
+            if ((rc = melissa_vb_lower_bound(h, &v))) return rc;
+            if (lb && nlb < lb_cap) lb[nlb] = v;
+            ++nlb;
+            if (v < lb_prev) fl |= MELISSA_FLAG_LB_DECREASED;               // :495-497
+            const bool conv = std::fabs(v - lb_prev) < epsilon_conv;        // :499-501
+            lb_prev = v;
+            if (conv) break;
+        }
+        if (i == vb_max_iter) fl |= MELISSA_FLAG_NOT_CONVERGED;             // :511-513
+    }
+    if ((rc = melissa_vb_fetch(h, W, W_Sigma, r_nk, delta, alpha, beta, pi_k))) return rc;
+    if (n_lb) *n_lb = nlb;
+    if (n_iter) *n_iter = it;
+    if (flags) *flags = fl;
+    return MELISSA_OK;
+}
+
+int melissa_impute(int32_t n_cells, int32_t n_regions, int32_t K, int32_t basis_kind, int32_t n_basis,
+                   const double *mus, double gamma, const double *W, const double *r_nk, int64_t n_pairs,
+                   const int64_t *pair_ptr, const int32_t *pair_cell, const int32_t *pair_region,
+                   const double *x, double *pred, int32_t device) {
+    if (n_cells <= 0 || n_regions <= 0 || K <= 0) return fail(MELISSA_ERR_ARG, "N, M and K must be positive");
+    if (basis_kind != MELISSA_BASIS_RBF) return fail(MELISSA_ERR_ARG, "only the RBF basis object is supported");
+    if (n_basis < 0 || n_basis + 1 > MAX_D || (n_basis > 0 && !mus))
+        return fail(MELISSA_ERR_ARG, "basis$M must be in 0..%d", MAX_D - 1);
+    if (n_pairs <= 0 || !pair_ptr || !pair_cell || !pair_region || !x || !pred || !W || !r_nk)
+        return fail(MELISSA_ERR_ARG, "empty or NULL arrays");
+    for (int64_t p = 0; p < n_pairs; ++p) {
+        if (pair_cell[p] < 0 || pair_cell[p] >= n_cells || pair_region[p] < 0 || pair_region[p] >= n_regions)
+            return fail(MELISSA_ERR_ARG, "test pair %lld: cell/region index out of range", (long long)p);
+        if (pair_ptr[p + 1] < pair_ptr[p]) return fail(MELISSA_ERR_ARG, "test pair_ptr must be non-decreasing");
+    }
+    CU(cudaSetDevice(device));
+    BasisDev basis{};
+    const int D = n_basis + 1;
+    basis.D = D; basis.gamma = gamma;
+    for (int j = 0; j < MAX_MUS; ++j) basis.mus[j] = j < n_basis ? mus[j] : 0.0;
+    int sm_count = 148;
+    cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device);
+    const int64_t nnz = pair_ptr[n_pairs];
+    const int64_t nW = (int64_t)n_regions * D * K, nr = (int64_t)n_cells * K;
+    int64_t *d_ptr = nullptr; int32_t *d_cell = nullptr, *d_reg = nullptr;
+    double *d_x = nullptr, *d_pred = nullptr, *d_W = nullptr, *d_r = nullptr;
+    int rc = MELISSA_OK;
+    auto cleanup = [&]() {
+        cudaFree(d_ptr); cudaFree(d_cell); cudaFree(d_reg); cudaFree(d_x); cudaFree(d_pred); cudaFree(d_W); cudaFree(d_r);
+    };
+    if ((rc = dev_alloc(&d_ptr, n_pairs + 1)) || (rc = dev_alloc(&d_cell, n_pairs)) ||
+        (rc = dev_alloc(&d_reg, n_pairs)) || (rc = dev_alloc(&d_x, nnz)) || (rc = dev_alloc(&d_pred, nnz)) ||
+        (rc = dev_alloc(&d_W, nW)) || (rc = dev_alloc(&d_r, nr))) {
+        cleanup();
+        return rc;
+    }
+    cudaMemcpyAsync(d_ptr, pair_ptr, (size_t)(n_pairs + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, nullptr);
+    cudaMemcpyAsync(d_cell, pair_cell, (size_t)n_pairs * sizeof(int32_t), cudaMemcpyHostToDevice, nullptr);
+    cudaMemcpyAsync(d_reg, pair_region, (size_t)n_pairs * sizeof(int32_t), cudaMemcpyHostToDevice, nullptr);
+    cudaMemcpyAsync(d_x, x, (size_t)nnz * sizeof(double), cudaMemcpyHostToDevice, nullptr);
+    cudaMemcpyAsync(d_W, W, (size_t)nW * sizeof(double), cudaMemcpyHostToDevice, nullptr);
+    cudaMemcpyAsync(d_r, r_nk, (size_t)nr * sizeof(double), cudaMemcpyHostToDevice, nullptr);
+    const int grid = grid_for(n_pairs, 128, sm_count, 16);
+    auto run = [&]() -> int {
+        DISPATCH_D(D, impute_kernel<DD><<<grid, 128>>>(d_ptr, d_cell, d_reg, d_x, d_W, d_r, d_pred, n_pairs,
+                                                      n_cells, n_regions, K, basis));
+        return MELISSA_OK;
+    };
+    if ((rc = run())) { cleanup(); return rc; }
+    cudaMemcpyAsync(pred, d_pred, (size_t)nnz * sizeof(double), cudaMemcpyDeviceToHost, nullptr);
+    const cudaError_t e = cudaDeviceSynchronize();
+    cleanup();
+    if (e != cudaSuccess) return fail(MELISSA_ERR_CUDA, "impute failed: %s", cudaGetErrorString(e));
+    return MELISSA_OK;
+}
+
+}  // extern "C"

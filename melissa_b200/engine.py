@@ -1,0 +1,163 @@
+"""Thin object wrapper over the C ABI: one `Engine` = one `melissa_handle`."""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import numpy as np
+
+from . import _lib
+from .data import MelissaData
+
+
+class _DeviceBuffer:
+    """Exposes a raw device pointer through __cuda_array_interface__ so torch can
+    alias it (used only to hand the reduction buffers to torch.distributed)."""
+
+    def __init__(self, ptr: int, n: int):
+        self.__cuda_array_interface__ = dict(shape=(int(n),), typestr="<f8", data=(int(ptr), False), version=2)
+
+
+class Engine:
+    """Packed observations on one GPU plus the state of one VB fit.
+
+    Mirrors the phases of the reference's melissa_inner (R/melissa_vb.R:232-529);
+    every method is one call into libmelissa_b200.so.
+    """
+
+    def __init__(self, data: MelissaData, basis: dict, device: int = 0, allow_empty_regions: bool = False):
+        lib = _lib.load()
+        if basis.get("kind", "rbf") != "rbf":
+            raise ValueError("only RBF basis objects are supported")
+        self.lib = lib
+        self.data = data
+        self.basis = basis
+        self.device = int(device)
+        self.N, self.M, self.P = int(data.N), int(data.M), data.P
+        self.D = int(basis["M"]) + 1
+        self.K = 0
+        mus = np.ascontiguousarray(basis["mus"], np.float64)
+        h = _lib.handle_t()
+        _lib.check(lib.melissa_pack(
+            self.N, self.M, self.P, _lib.ptr(np.ascontiguousarray(data.pair_ptr, np.int64), _lib.c_i64),
+            _lib.ptr(np.ascontiguousarray(data.pair_cell, np.int32), _lib.c_i32),
+            _lib.ptr(np.ascontiguousarray(data.pair_region, np.int32), _lib.c_i32),
+            _lib.ptr(np.ascontiguousarray(data.x, np.float64), _lib.c_dbl),
+            _lib.ptr(np.ascontiguousarray(data.y, np.uint8), C.c_uint8),
+            1, int(basis["M"]), _lib.ptr(mus, _lib.c_dbl) if mus.size else None, float(basis["gamma"]),
+            self.device, int(bool(allow_empty_regions)), C.byref(h)))
+        self.h = h
+
+    # -- lifetime -----------------------------------------------------------
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.melissa_free(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # -- one-shot fit (the loop runs inside the library) -------------------------
+    def run(self, K, w0, delta_0, alpha_0=0.5, beta_0=None, vb_max_iter=300, epsilon_conv=1e-5, lb_every=10):
+        K = int(K)
+        w0 = self._check_w(w0, K)
+        delta_0 = np.ascontiguousarray(delta_0, np.float64)
+        if delta_0.shape != (K,):
+            raise ValueError("delta_0 must have length K")
+        cap = (int(vb_max_iter) // int(lb_every)) + 3
+        out = self._alloc_outputs(K)
+        lb = np.empty(cap, np.float64)
+        n_lb, n_iter, flags = _lib.c_i32(0), _lib.c_i32(0), _lib.c_i32(0)
+        _lib.check(self.lib.melissa_vb_run(
+            self.h, K, _lib.ptr(w0, _lib.c_dbl), _lib.ptr(delta_0, _lib.c_dbl), float(alpha_0),
+            float("nan") if beta_0 is None else float(beta_0), int(vb_max_iter), float(epsilon_conv),
+            int(lb_every), *[_lib.ptr(out[k], _lib.c_dbl) for k in ("W", "W_Sigma", "r_nk", "delta", "alpha",
+                                                                    "beta", "pi_k")],
+            _lib.ptr(lb, _lib.c_dbl), cap, C.byref(n_lb), C.byref(n_iter), C.byref(flags)))
+        self.K = K
+        res = self._shape_outputs(out, K)
+        res.update(lb=lb[:n_lb.value].copy(), n_iter=n_iter.value, flags=flags.value)
+        return res
+
+    # -- step-wise fit ---------------------------------------------------------
+    def begin(self, K, w0, delta_0, alpha_0=0.5, beta_0=None, n_cells_total=None, stream=0):
+        K = int(K)
+        w0 = self._check_w(w0, K)
+        delta_0 = np.ascontiguousarray(delta_0, np.float64)
+        if delta_0.shape != (K,):
+            raise ValueError("delta_0 must have length K")
+        _lib.check(self.lib.melissa_vb_begin(
+            self.h, K, _lib.ptr(w0, _lib.c_dbl), _lib.ptr(delta_0, _lib.c_dbl), float(alpha_0),
+            float("nan") if beta_0 is None else float(beta_0),
+            int(self.N if n_cells_total is None else n_cells_total), C.c_void_p(int(stream) or None)))
+        self.K = K
+
+    def phase_a(self):
+        _lib.check(self.lib.melissa_vb_phase_a(self.h))
+
+    def phase_b(self, with_lb: bool):
+        _lib.check(self.lib.melissa_vb_phase_b(self.h, int(bool(with_lb))))
+
+    def lower_bound(self) -> float:
+        v = _lib.c_dbl(0.0)
+        _lib.check(self.lib.melissa_vb_lower_bound(self.h, C.byref(v)))
+        return v.value
+
+    def _tensor(self, fn):
+        import torch
+        p, n = C.c_void_p(), _lib.c_i64(0)
+        _lib.check(fn(self.h, C.byref(p), C.byref(n)))
+        return torch.as_tensor(_DeviceBuffer(p.value, n.value), device=f"cuda:{self.device}")
+
+    def reduce_tensor(self):
+        """torch view of the sufficient-statistics buffer (all-reduce SUM between phase_a and phase_b)."""
+        return self._tensor(self.lib.melissa_vb_reduce_buffer)
+
+    def lb_tensor(self):
+        """torch view of the lb_pz_qz partial (all-reduce SUM before lower_bound)."""
+        return self._tensor(self.lib.melissa_vb_lb_buffer)
+
+    def fetch(self):
+        out = self._alloc_outputs(self.K)
+        _lib.check(self.lib.melissa_vb_fetch(self.h, *[_lib.ptr(out[k], _lib.c_dbl) for k in
+                                                       ("W", "W_Sigma", "r_nk", "delta", "alpha", "beta", "pi_k")]))
+        return self._shape_outputs(out, self.K)
+
+    def fetch_HtEz(self):
+        out = np.empty((self.P, self.D), np.float64)
+        _lib.check(self.lib.melissa_vb_fetch_HtEz(self.h, _lib.ptr(out, _lib.c_dbl)))
+        return out
+
+    def sync(self):
+        _lib.check(self.lib.melissa_sync(self.h))
+
+    def launch_count(self) -> int:
+        return int(self.lib.melissa_launch_count(self.h))
+
+    # -- helpers ----------------------------------------------------------------
+    def _check_w(self, w0, K):
+        w0 = np.asarray(w0, np.float64)
+        if w0.shape != (self.M, self.D, K):
+            raise ValueError(f"w must have shape (M, D, K) = {(self.M, self.D, K)}, got {w0.shape}")
+        return np.asfortranarray(w0).ravel(order="F").copy()      # R array layout
+
+    def _alloc_outputs(self, K):
+        M, D, N = self.M, self.D, self.N
+        return dict(W=np.empty(M * D * K), W_Sigma=np.empty(K * M * D * D), r_nk=np.empty(N * K),
+                    delta=np.empty(K), alpha=np.empty(K), beta=np.empty(K), pi_k=np.empty(K))
+
+    def _shape_outputs(self, out, K):
+        M, D, N = self.M, self.D, self.N
+        return dict(W=out["W"].reshape((M, D, K), order="F"),
+                    W_Sigma=out["W_Sigma"].reshape(K, M, D, D),
+                    r_nk=out["r_nk"].reshape((N, K), order="F"),
+                    delta=out["delta"], alpha=out["alpha"], beta=out["beta"], pi_k=out["pi_k"])

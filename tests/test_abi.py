@@ -1,0 +1,56 @@
+"""CPU: the C-ABI library builds, loads and exports every symbol the header declares."""
+import ctypes
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def header_functions():
+    src = open(os.path.join(ROOT, "include", "melissa_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(melissa_[a-zA-Z0-9_]+)\s*\(", src)))
+
+
+def test_header_declares_the_boundary():
+    names = header_functions()
+    for must in ("melissa_pack", "melissa_vb_run", "melissa_free", "melissa_last_error", "melissa_impute"):
+        assert must in names
+
+
+def test_library_exports_every_declared_symbol():
+    from melissa_b200 import _lib
+    from melissa_b200.build import build_library
+    build_library()
+    lib = _lib.load()
+    names = header_functions()
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in the header but not exported"
+    assert sorted(_lib.SIGNATURES) == names, "ctypes signature table and header disagree"
+    assert lib.melissa_abi_version() == 1
+
+
+def test_argument_errors_do_not_need_a_gpu():
+    # validation happens before the first CUDA call, and mirrors the reference's checks
+    import numpy as np
+    from melissa_b200 import _lib
+    lib = _lib.load()
+    h = _lib.handle_t()
+    ptr = np.array([0, 2, 4], np.int64)
+    cell = np.array([0, 2], np.int32)          # cell 1 has no covered region
+    reg = np.array([0, 0], np.int32)
+    x = np.zeros(4)
+    y = np.zeros(4, np.uint8)
+    mus = np.array([-0.5, 0, 0.5])
+    rc = lib.melissa_pack(3, 1, 2, _lib.ptr(ptr, _lib.c_i64), _lib.ptr(cell, _lib.c_i32), _lib.ptr(reg, _lib.c_i32),
+                          _lib.ptr(x, _lib.c_dbl), _lib.ptr(y, ctypes.c_uint8), 1, 3, _lib.ptr(mus, _lib.c_dbl), 2.25,
+                          0, 0, ctypes.byref(h))
+    assert rc == 1
+    assert b"No coverage across all regions" in lib.melissa_last_error()   # R/utils.R:69-71
+    rc = lib.melissa_pack(3, 1, 2, _lib.ptr(ptr, _lib.c_i64), _lib.ptr(cell, _lib.c_i32), _lib.ptr(reg, _lib.c_i32),
+                          _lib.ptr(x, _lib.c_dbl), _lib.ptr(y, ctypes.c_uint8), 2, 3, _lib.ptr(mus, _lib.c_dbl), 2.25,
+                          0, 0, ctypes.byref(h))
+    assert rc == 1 and b"RBF" in lib.melissa_last_error()
+    assert lib.melissa_vb_phase_a(None) == 3
