@@ -77,6 +77,18 @@ int melissa_pack(int32_t n_cells, int32_t n_regions, int64_t n_pairs,
                  int32_t basis_kind, int32_t n_basis, const double *mus, double gamma,
                  int32_t device, int32_t allow_empty_regions, melissa_handle **out);
 
+/*
+ * Same as melissa_pack, but the five observation arrays are DEVICE pointers on
+ * `device` (data generated or already resident there).  x / y are copied device to
+ * device; only the index lists visit the host (to be validated and inverted).
+ * No counterpart in the reference (its data always start as R lists).
+ */
+int melissa_pack_device(int32_t n_cells, int32_t n_regions, int64_t n_pairs,
+                        const int64_t *pair_ptr, const int32_t *pair_cell, const int32_t *pair_region,
+                        const double *x, const uint8_t *y,
+                        int32_t basis_kind, int32_t n_basis, const double *mus, double gamma,
+                        int32_t device, int32_t allow_empty_regions, melissa_handle **out);
+
 /* Release every device and host resource behind the handle (NULL is a no-op). */
 int melissa_free(melissa_handle *h);
 
@@ -147,6 +159,22 @@ int melissa_vb_fetch_HtEz(melissa_handle *h, double *out);
 
 /* Block until all work queued on the handle's stream is done. */
 int melissa_sync(melissa_handle *h);
+
+/*
+ * Optional per-kernel timing with CUDA events on the handle's stream (what
+ * bench.py's roofline figure is measured with; the reference's only equivalent is
+ * wrapping whole calls in microbenchmark, inst/examples/model-efficiency/).
+ * melissa_profile_enable(h, 1) starts recording one event pair per launch,
+ * (h, 0) stops and drops them; melissa_profile_read sums one kernel's launches.
+ */
+#define MELISSA_KERNEL_SWEEP 0     /* per-CpG E[z] sweep + next E-step terms */
+#define MELISSA_KERNEL_RESP 1      /* responsibilities */
+#define MELISSA_KERNEL_CONTRACT 2  /* r-weighted sufficient statistics */
+#define MELISSA_KERNEL_SOLVE 3     /* batched D x D solves */
+#define MELISSA_KERNEL_SCALARS 4   /* beta / delta / E[log pi] */
+#define MELISSA_KERNEL_LB 5        /* lower-bound assembly */
+int melissa_profile_enable(melissa_handle *h, int32_t on);
+int melissa_profile_read(melissa_handle *h, int32_t kernel_id, double *total_ms, int64_t *count);
 
 /* Number of kernels this handle has launched so far (bench.py's gpu_launches). */
 int64_t melissa_launch_count(const melissa_handle *h);

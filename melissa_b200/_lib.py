@@ -20,7 +20,11 @@ SIGNATURES = {
     "melissa_abi_version": (C.c_int, []),
     "melissa_pack": (C.c_int, [c_i32, c_i32, c_i64, p_i64, p_i32, p_i32, p_dbl, p_u8, c_i32, c_i32, p_dbl, c_dbl,
                                c_i32, c_i32, C.POINTER(handle_t)]),
+    "melissa_pack_device": (C.c_int, [c_i32, c_i32, c_i64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                      c_i32, c_i32, p_dbl, c_dbl, c_i32, c_i32, C.POINTER(handle_t)]),
     "melissa_free": (C.c_int, [handle_t]),
+    "melissa_profile_enable": (C.c_int, [handle_t, c_i32]),
+    "melissa_profile_read": (C.c_int, [handle_t, c_i32, p_dbl, p_i64]),
     "melissa_vb_run": (C.c_int, [handle_t, c_i32, p_dbl, p_dbl, c_dbl, c_dbl, c_i32, c_dbl, c_i32,
                                  p_dbl, p_dbl, p_dbl, p_dbl, p_dbl, p_dbl, p_dbl, p_dbl, c_i32,
                                  p_i32, p_i32, p_i32]),

@@ -95,6 +95,10 @@ struct melissa_handle {
     int64_t launches = 0;
     bool begun = false;
     int sm_count = 148;
+    // optional per-kernel timing (CUDA events on h->stream), see melissa_profile_*
+    bool prof_on = false;
+    std::vector<cudaEvent_t> prof_ev;      // start/stop pairs
+    std::vector<int> prof_id;
 };
 
 namespace {
@@ -583,6 +587,22 @@ __global__ void impute_kernel(const int64_t *__restrict__ pair_ptr, const int32_
     }
 }
 
+void prof_begin(melissa_handle *h, int id) {
+    h->launches++;
+    if (!h->prof_on) return;
+    cudaEvent_t a, b;
+    cudaEventCreate(&a);
+    cudaEventCreate(&b);
+    h->prof_ev.push_back(a);
+    h->prof_ev.push_back(b);
+    h->prof_id.push_back(id);
+    cudaEventRecord(a, h->stream);
+}
+void prof_end(melissa_handle *h) {
+    if (!h->prof_on) return;
+    cudaEventRecord(h->prof_ev.back(), h->stream);
+}
+
 // ---------------------------------------------------------------------------
 // launch helpers
 // ---------------------------------------------------------------------------
@@ -606,6 +626,7 @@ int grid_for(int64_t work, int block, int sm_count, int per_sm) {
 
 int launch_sweep(melissa_handle *h, bool with_lb, bool uniform_r) {
     const int block = 128;
+    prof_begin(h, MELISSA_KERNEL_SWEEP);
     const int grid = grid_for(h->P, block, h->sm_count, 16);
 #define SWEEP(LB_, UNI_)                                                                        \
     DISPATCH_D(h->D, sweep_kernel<DD, LB_, UNI_><<<grid, block, 0, h->stream>>>(                 \
@@ -616,7 +637,7 @@ int launch_sweep(melissa_handle *h, bool with_lb, bool uniform_r) {
     else if (uniform_r) { SWEEP(false, true) }
     else { SWEEP(false, false) }
 #undef SWEEP
-    h->launches++;
+    prof_end(h);
     CU(cudaGetLastError());
     return MELISSA_OK;
 }
@@ -630,6 +651,7 @@ int launch_contract(melissa_handle *h) {
     const dim3 grid(h->M, (slices + 3) / 4);
     const int block = 128;
     double *acc = h->red;
+    prof_begin(h, MELISSA_KERNEL_CONTRACT);
 #define CONTRACT(J_, KC_)                                                                     \
     contract_kernel<J_, KC_><<<grid, block, 0, h->stream>>>(h->reg_ptr, h->reg_pair, h->reg_cell, \
                                                           h->stats, h->r, acc, h->K, h->R)
@@ -644,7 +666,7 @@ int launch_contract(melissa_handle *h) {
         return fail(MELISSA_ERR_ARG, "record length %d not supported", h->R);
     }
 #undef CONTRACT
-    h->launches++;
+    prof_end(h);
     CU(cudaGetLastError());
     return MELISSA_OK;
 }
@@ -663,6 +685,13 @@ void free_fit(melissa_handle *h) {
     h->begun = false;
 }
 
+__global__ void count_bad_y_kernel(const uint8_t *__restrict__ y, int64_t n, unsigned long long *bad) {
+    unsigned long long c = 0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        c += y[i] > 1;
+    if (c) atomicAdd(bad, c);
+}
+
 }  // namespace
 
 // ===========================================================================
@@ -673,11 +702,29 @@ extern "C" {
 const char *melissa_last_error(void) { return g_err.c_str(); }
 int melissa_abi_version(void) { return 1; }
 
-int melissa_pack(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const int64_t *pair_ptr,
-                 const int32_t *pair_cell, const int32_t *pair_region, const double *x,
-                 const uint8_t *y, int32_t basis_kind, int32_t n_basis, const double *mus,
-                 double gamma, int32_t device, int32_t allow_empty_regions, melissa_handle **out) {
+static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const int64_t *pair_ptr_in,
+                     const int32_t *pair_cell_in, const int32_t *pair_region_in, const double *x,
+                     const uint8_t *y, int32_t basis_kind, int32_t n_basis, const double *mus,
+                     double gamma, int32_t device, int32_t allow_empty_regions, bool on_device,
+                     melissa_handle **out) {
     if (!out) return fail(MELISSA_ERR_ARG, "out is NULL");
+    const int64_t *pair_ptr = pair_ptr_in;
+    const int32_t *pair_cell = pair_cell_in, *pair_region = pair_region_in;
+    std::vector<int64_t> host_ptr;
+    std::vector<int32_t> host_cell, host_region;
+    if (on_device && n_pairs > 0 && pair_ptr_in && pair_cell_in && pair_region_in) {
+        // the index lists are validated and inverted on the host; x / y never leave the device
+        CU(cudaSetDevice(device));
+        host_ptr.resize((size_t)n_pairs + 1);
+        host_cell.resize((size_t)n_pairs);
+        host_region.resize((size_t)n_pairs);
+        CU(cudaMemcpy(host_ptr.data(), pair_ptr_in, host_ptr.size() * sizeof(int64_t), cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(host_cell.data(), pair_cell_in, host_cell.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(host_region.data(), pair_region_in, host_region.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
+        pair_ptr = host_ptr.data();
+        pair_cell = host_cell.data();
+        pair_region = host_region.data();
+    }
     *out = nullptr;
     if (n_cells <= 0 || n_regions <= 0) return fail(MELISSA_ERR_ARG, "N > 0 and M > 0 are required");
     if (n_pairs <= 0 || !pair_ptr || !pair_cell || !pair_region || !x || !y)
@@ -718,8 +765,10 @@ int melissa_pack(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const int6
     if (cells_seen != n_cells)
         return fail(MELISSA_ERR_ARG, "cell %d: No coverage across all regions. This cell should be discarded!", cells_seen);
     const int64_t nnz = pair_ptr[P];
-    for (int64_t i = 0; i < nnz; ++i)
-        if (y[i] > 1) return fail(MELISSA_ERR_ARG, "methylation state y[%lld] is not 0/1", (long long)i);
+    if (!on_device) {
+        for (int64_t i = 0; i < nnz; ++i)
+            if (y[i] > 1) return fail(MELISSA_ERR_ARG, "methylation state y[%lld] is not 0/1", (long long)i);
+    }
     if (!allow_empty_regions)
         for (int32_t m = 0; m < n_regions; ++m)
             if (reg_cnt[(size_t)m + 1] == 0)
@@ -756,13 +805,22 @@ int melissa_pack(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const int6
     if ((rc = dev_alloc(&h->reg_cell, P))) return bail(rc);
     if ((rc = dev_alloc(&h->stats, P * h->R))) return bail(rc);
 #define H2D(dst, src, n, Tp)                                                                          \
-    if (cudaMemcpyAsync(dst, src, (size_t)(n) * sizeof(Tp), cudaMemcpyHostToDevice, nullptr) != cudaSuccess) \
-        return bail(fail(MELISSA_ERR_CUDA, "H2D copy of " #src " failed: %s", cudaGetErrorString(cudaGetLastError())))
-    H2D(h->pair_ptr, pair_ptr, P + 1, int64_t);
-    H2D(h->pair_cell, pair_cell, P, int32_t);
-    H2D(h->pair_region, pair_region, P, int32_t);
+    if (cudaMemcpyAsync(dst, src, (size_t)(n) * sizeof(Tp), cudaMemcpyDefault, nullptr) != cudaSuccess)    \
+        return bail(fail(MELISSA_ERR_CUDA, "copy of " #src " failed: %s", cudaGetErrorString(cudaGetLastError())))
+    H2D(h->pair_ptr, pair_ptr_in, P + 1, int64_t);
+    H2D(h->pair_cell, pair_cell_in, P, int32_t);
+    H2D(h->pair_region, pair_region_in, P, int32_t);
     H2D(h->x, x, nnz, double);
     H2D(h->y, y, nnz, uint8_t);
+    if (on_device) {
+        unsigned long long *bad = nullptr, bad_h = 0;
+        if ((rc = dev_alloc(&bad, 1))) return bail(rc);
+        cudaMemsetAsync(bad, 0, sizeof(unsigned long long), nullptr);
+        count_bad_y_kernel<<<grid_for(nnz, 256, h->sm_count, 8), 256>>>(h->y, nnz, bad);
+        cudaMemcpy(&bad_h, bad, sizeof bad_h, cudaMemcpyDeviceToHost);
+        cudaFree(bad);
+        if (bad_h) return bail(fail(MELISSA_ERR_ARG, "%llu methylation states are not 0/1", bad_h));
+    }
     H2D(h->reg_ptr, reg_cnt.data(), n_regions + 1, int64_t);
     H2D(h->reg_pair, reg_pair.data(), P, int32_t);
     H2D(h->reg_cell, reg_cell.data(), P, int32_t);
@@ -782,9 +840,54 @@ int melissa_pack(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const int6
     return MELISSA_OK;
 }
 
+int melissa_pack(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const int64_t *pair_ptr,
+                 const int32_t *pair_cell, const int32_t *pair_region, const double *x,
+                 const uint8_t *y, int32_t basis_kind, int32_t n_basis, const double *mus,
+                 double gamma, int32_t device, int32_t allow_empty_regions, melissa_handle **out) {
+    return pack_impl(n_cells, n_regions, n_pairs, pair_ptr, pair_cell, pair_region, x, y, basis_kind, n_basis, mus,
+                     gamma, device, allow_empty_regions, false, out);
+}
+
+int melissa_pack_device(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const int64_t *pair_ptr,
+                        const int32_t *pair_cell, const int32_t *pair_region, const double *x,
+                        const uint8_t *y, int32_t basis_kind, int32_t n_basis, const double *mus,
+                        double gamma, int32_t device, int32_t allow_empty_regions, melissa_handle **out) {
+    return pack_impl(n_cells, n_regions, n_pairs, pair_ptr, pair_cell, pair_region, x, y, basis_kind, n_basis, mus,
+                     gamma, device, allow_empty_regions, true, out);
+}
+
+int melissa_profile_enable(melissa_handle *h, int32_t on) {
+    if (!h) return fail(MELISSA_ERR_ARG, "handle is NULL");
+    cudaSetDevice(h->device);
+    for (cudaEvent_t e : h->prof_ev) cudaEventDestroy(e);
+    h->prof_ev.clear();
+    h->prof_id.clear();
+    h->prof_on = on != 0;
+    return MELISSA_OK;
+}
+
+int melissa_profile_read(melissa_handle *h, int32_t kernel_id, double *total_ms, int64_t *count) {
+    if (!h) return fail(MELISSA_ERR_ARG, "handle is NULL");
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->stream));
+    double tot = 0.0;
+    int64_t cnt = 0;
+    for (size_t i = 0; i < h->prof_id.size(); ++i) {
+        if (h->prof_id[i] != kernel_id) continue;
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, h->prof_ev[2 * i], h->prof_ev[2 * i + 1]));
+        tot += ms;
+        ++cnt;
+    }
+    if (total_ms) *total_ms = tot;
+    if (count) *count = cnt;
+    return MELISSA_OK;
+}
+
 int melissa_free(melissa_handle *h) {
     if (!h) return MELISSA_OK;
     cudaSetDevice(h->device);
+    for (cudaEvent_t e : h->prof_ev) cudaEventDestroy(e);
     free_fit(h);
     cudaFree(h->pair_ptr); cudaFree(h->pair_cell); cudaFree(h->pair_region); cudaFree(h->x);
     cudaFree(h->y); cudaFree(h->reg_ptr); cudaFree(h->reg_pair); cudaFree(h->reg_cell);
@@ -859,9 +962,10 @@ int melissa_vb_phase_a(melissa_handle *h) {
     const int64_t MK = (int64_t)h->M * h->K;
     CU(cudaMemsetAsync(h->red, 0, (size_t)h->red_len * sizeof(double), h->stream));
     double *colsum = h->red + MK * h->R, *rlogr = colsum + h->K;
+    prof_begin(h, MELISSA_KERNEL_RESP);
     resp_kernel<<<(h->N + 127) / 128, 128, 0, h->stream>>>(h->log_rho, h->sc.elogpi, h->r, h->log_r, colsum,
                                                           rlogr, h->sc.Eww_acc, h->sc.logdet_acc, h->N, h->K);
-    h->launches++;
+    prof_end(h);
     CU(cudaGetLastError());
     return launch_contract(h);
 }
@@ -880,11 +984,13 @@ int melissa_vb_phase_b(melissa_handle *h, int32_t with_lb) {
             return MELISSA_OK;
         };
         int rc;
+        prof_begin(h, MELISSA_KERNEL_SOLVE);
         if ((rc = run())) return rc;
-        h->launches++;
+        prof_end(h);
     }
+    prof_begin(h, MELISSA_KERNEL_SCALARS);
     scalars_kernel<<<1, 32, 0, h->stream>>>(h->sc, colsum, h->K, h->alpha_k, h->beta_0, (double)h->N_total, 0);
-    h->launches++;
+    prof_end(h);
     CU(cudaGetLastError());
     if (with_lb) CU(cudaMemsetAsync(h->lbbuf, 0, 2 * sizeof(double), h->stream));
     return launch_sweep(h, with_lb != 0, false);
@@ -895,9 +1001,10 @@ int melissa_vb_lower_bound(melissa_handle *h, double *lb_out) {
     CU(cudaSetDevice(h->device));
     const int64_t MK = (int64_t)h->M * h->K;
     double *colsum = h->red + MK * h->R, *rlogr = colsum + h->K;
+    prof_begin(h, MELISSA_KERNEL_LB);
     lb_kernel<<<1, 32, 0, h->stream>>>(h->sc, colsum, rlogr, h->lbbuf, h->K, h->M, h->D, h->alpha_0, h->alpha_k,
                                        h->beta_0);
-    h->launches++;
+    prof_end(h);
     CU(cudaGetLastError());
     double v = 0.0;
     CU(cudaMemcpyAsync(&v, h->sc.lb_out, sizeof(double), cudaMemcpyDeviceToHost, h->stream));

@@ -25,7 +25,7 @@ class Engine:
     every method is one call into libmelissa_b200.so.
     """
 
-    def __init__(self, data: MelissaData, basis: dict, device: int = 0, allow_empty_regions: bool = False):
+    def __init__(self, data, basis: dict, device: int = 0, allow_empty_regions: bool = False):
         lib = _lib.load()
         if basis.get("kind", "rbf") != "rbf":
             raise ValueError("only RBF basis objects are supported")
@@ -33,11 +33,26 @@ class Engine:
         self.data = data
         self.basis = basis
         self.device = int(device)
-        self.N, self.M, self.P = int(data.N), int(data.M), data.P
         self.D = int(basis["M"]) + 1
         self.K = 0
         mus = np.ascontiguousarray(basis["mus"], np.float64)
         h = _lib.handle_t()
+        if isinstance(data, dict) and data.get("on_device"):
+            # torch CUDA tensors already resident on `device` (melissa_pack_device)
+            t = data
+            self.N, self.M, self.P = int(t["N"]), int(t["M"]), int(t["pair_cell"].shape[0])
+            for k, dt in (("pair_ptr", "int64"), ("pair_cell", "int32"), ("pair_region", "int32"),
+                          ("x", "float64"), ("y", "uint8")):
+                if str(t[k].dtype) != "torch." + dt or not t[k].is_contiguous() or t[k].device.index != self.device:
+                    raise ValueError(f"{k}: need a contiguous {dt} tensor on cuda:{self.device}")
+            _lib.check(lib.melissa_pack_device(
+                self.N, self.M, self.P, t["pair_ptr"].data_ptr(), t["pair_cell"].data_ptr(),
+                t["pair_region"].data_ptr(), t["x"].data_ptr(), t["y"].data_ptr(), 1, int(basis["M"]),
+                _lib.ptr(mus, _lib.c_dbl) if mus.size else None, float(basis["gamma"]), self.device,
+                int(bool(allow_empty_regions)), C.byref(h)))
+            self.h = h
+            return
+        self.N, self.M, self.P = int(data.N), int(data.M), data.P
         _lib.check(lib.melissa_pack(
             self.N, self.M, self.P, _lib.ptr(np.ascontiguousarray(data.pair_ptr, np.int64), _lib.c_i64),
             _lib.ptr(np.ascontiguousarray(data.pair_cell, np.int32), _lib.c_i32),
@@ -142,6 +157,20 @@ class Engine:
 
     def launch_count(self) -> int:
         return int(self.lib.melissa_launch_count(self.h))
+
+    KERNELS = dict(sweep=0, resp=1, contract=2, solve=3, scalars=4, lb=5)
+
+    def profile(self, on: bool):
+        _lib.check(self.lib.melissa_profile_enable(self.h, int(bool(on))))
+
+    def profile_read(self):
+        """{kernel: (total ms, launches)} since profile(True)."""
+        out = {}
+        for name, kid in self.KERNELS.items():
+            ms, cnt = _lib.c_dbl(0.0), _lib.c_i64(0)
+            _lib.check(self.lib.melissa_profile_read(self.h, kid, C.byref(ms), C.byref(cnt)))
+            out[name] = (ms.value, cnt.value)
+        return out
 
     # -- helpers ----------------------------------------------------------------
     def _check_w(self, w0, K):

@@ -112,3 +112,19 @@ def test_ari_and_auc_known_answers():
     assert abs(mo.adjusted_rand_index([0, 0, 1, 1], [0, 1, 0, 1]) - (-0.5)) < 1e-12
     perf = mo.eval_imputation_performance([1, 1, 0, 0], [0.9, 0.4, 0.6, 0.1])
     assert abs(perf["auc"] - 0.75) < 1e-12
+
+
+def test_c_restatement_matches_numpy_oracle(c1, c2):
+    # oracle/melissa_oracle.c (the timed CPU baseline) against the NumPy oracle
+    import c_oracle
+    for threads in (1, 2):
+        o = c_oracle.vb_run(c1, 3, c1["basis"], c1["w0_k3"], c1["k3_delta_0"], vb_max_iter=int(c1["k3_iters"]),
+                            n_threads=threads)
+        np.testing.assert_allclose(o["lb"][1:], c1["k3_lb"][1:] + math.log(math.factorial(3)), rtol=1e-11)
+        np.testing.assert_allclose(o["r_nk"], c1["k3_r_nk"], atol=1e-9)
+        np.testing.assert_allclose(o["W"], c1["k3_W"], atol=1e-8)
+        np.testing.assert_allclose(o["W_Sigma"], c1["k3_W_Sigma"], atol=1e-9)
+        assert o["flags"] == int(c1["k3_flags"]) and o["n_iter"] == int(c1["k3_n_iter"])
+    train = subset(c2, c2["is_train"])
+    o = c_oracle.vb_run(train, 4, c2["basis"], c2["w0"], c2["delta_0"], vb_max_iter=20)
+    np.testing.assert_allclose(o["lb"][1:], (c2["lb"][1:] + math.log(math.factorial(4)))[:2], rtol=1e-11)
