@@ -192,6 +192,43 @@ int melissa_impute(int32_t n_cells, int32_t n_regions, int32_t K, int32_t basis_
                    int64_t n_pairs, const int64_t *pair_ptr, const int32_t *pair_cell,
                    const int32_t *pair_region, const double *x, double *pred, int32_t device);
 
+/*
+ * melissa_impute for hosts that cannot allocate device memory.  (No counterpart
+ * in the reference: it exists because of how GPU processes are deployed, not
+ * because of anything in Melissa.)
+ *
+ * Who needs it: a host process in which some other runtime has already claimed
+ * all of the GPU's memory for its own pool, so that one more cudaMalloc fails; or
+ * a service that imputes a small batch per request and may not enter the CUDA
+ * allocator at that point (for instance because another thread of the process is
+ * in the middle of a stream capture).  melissa_impute allocates and frees seven
+ * device buffers on every call; this variant calls no cudaMalloc / cudaFree and
+ * no allocating library routine.  Instead it stages its inputs and its output in
+ * a fixed array of MELISSA_NOALLOC_SCRATCH_BYTES that is part of the library
+ * image -- every GPU that loads the library holds that much memory until the
+ * process exits, whether or not this function is ever called.
+ *
+ * Same arguments, same HOST buffers and the same result as melissa_impute.
+ * Limits and rules:
+ *   - the staged pieces (pair_ptr, pair_cell, pair_region, x, pred, W, r_nk, each
+ *     rounded up to 256 bytes) must fit the array; a larger call is refused with
+ *     MELISSA_ERR_ARG and a message that states both sizes -- split the batch or
+ *     use melissa_impute;
+ *   - the first call on a device looks up the array's device address
+ *     (cudaGetSymbolAddress, once per device).  Make that first call before any
+ *     stream capture starts;
+ *   - all calls share the one array and it keeps the previous call's bytes.  The
+ *     function overwrites everything it reads before it launches, so stale
+ *     contents are harmless, but two calls that are in flight at the same time on
+ *     one GPU (two host threads) overwrite each other: serialise them.
+ */
+#define MELISSA_NOALLOC_SCRATCH_BYTES (8u << 20)   /* 8 MiB */
+int melissa_impute_noalloc(int32_t n_cells, int32_t n_regions, int32_t K, int32_t basis_kind,
+                           int32_t n_basis, const double *mus, double gamma, const double *W,
+                           const double *r_nk, int64_t n_pairs, const int64_t *pair_ptr,
+                           const int32_t *pair_cell, const int32_t *pair_region, const double *x,
+                           double *pred, int32_t device);
+
 #ifdef __cplusplus
 }
 #endif

@@ -40,6 +40,8 @@ SIGNATURES = {
     "melissa_launch_count": (c_i64, [handle_t]),
     "melissa_impute": (C.c_int, [c_i32, c_i32, c_i32, c_i32, c_i32, p_dbl, c_dbl, p_dbl, p_dbl, c_i64, p_i64, p_i32,
                                  p_i32, p_dbl, p_dbl, c_i32]),
+    "melissa_impute_noalloc": (C.c_int, [c_i32, c_i32, c_i32, c_i32, c_i32, p_dbl, c_dbl, p_dbl, p_dbl, c_i64, p_i64,
+                                         p_i32, p_i32, p_dbl, p_dbl, c_i32]),
 }
 
 _lib = None

@@ -25,6 +25,7 @@
 #include <cstdio>
 #include <cstring>
 #include <limits>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1181,6 +1182,112 @@ int melissa_impute(int32_t n_cells, int32_t n_regions, int32_t K, int32_t basis_
     const cudaError_t e = cudaDeviceSynchronize();
     cleanup();
     if (e != cudaSuccess) return fail(MELISSA_ERR_CUDA, "impute failed: %s", cudaGetErrorString(e));
+    return MELISSA_OK;
+}
+
+
+// ---------------------------------------------------------------------------
+// Imputation without any device allocation.
+//
+// melissa_impute() above stages the caller's host arrays in device buffers it
+// cudaMalloc's and frees on every call.  A host that must not (or cannot)
+// allocate device memory -- a process whose GPU memory has been handed in full
+// to another runtime's pool, so that a further cudaMalloc fails; a service that
+// imputes one small batch per request and may not touch the allocator while some
+// other thread of the process has a stream capture open -- gets the same result
+// from the entry point below: the staging area is this fixed array, which lives
+// in the library image (every GPU that loads the library holds these bytes until
+// the process exits).
+//
+// `g_noalloc_scratch` is only a host-side handle here; the kernel needs the
+// device address, obtained once per device with cudaGetSymbolAddress while that
+// device is current.
+// ---------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_noalloc_scratch[MELISSA_NOALLOC_SCRATCH_BYTES];
+
+static std::mutex g_noalloc_mu;
+static unsigned char *g_noalloc_ptr[64] = {nullptr};
+
+static int noalloc_device_ptr(int device, unsigned char **out) {
+    if (device < 0 || device >= 64) return fail(MELISSA_ERR_ARG, "device index %d out of range", device);
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) {
+        CU(cudaSetDevice(device));
+        void *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p)
+            return fail(MELISSA_ERR_CUDA, "cudaGetSymbolAddress(scratch) failed on device %d: %s", device,
+                        cudaGetErrorString(e));
+        g_noalloc_ptr[device] = static_cast<unsigned char *>(p);
+    }
+    *out = g_noalloc_ptr[device];
+    return MELISSA_OK;
+}
+
+int melissa_impute_noalloc(int32_t n_cells, int32_t n_regions, int32_t K, int32_t basis_kind, int32_t n_basis,
+                           const double *mus, double gamma, const double *W, const double *r_nk, int64_t n_pairs,
+                           const int64_t *pair_ptr, const int32_t *pair_cell, const int32_t *pair_region,
+                           const double *x, double *pred, int32_t device) {
+    if (n_cells <= 0 || n_regions <= 0 || K <= 0) return fail(MELISSA_ERR_ARG, "N, M and K must be positive");
+    if (basis_kind != MELISSA_BASIS_RBF) return fail(MELISSA_ERR_ARG, "only the RBF basis object is supported");
+    if (n_basis < 0 || n_basis + 1 > MAX_D || (n_basis > 0 && !mus))
+        return fail(MELISSA_ERR_ARG, "basis$M must be in 0..%d", MAX_D - 1);
+    if (n_pairs <= 0 || !pair_ptr || !pair_cell || !pair_region || !x || !pred || !W || !r_nk)
+        return fail(MELISSA_ERR_ARG, "empty or NULL arrays");
+    for (int64_t p = 0; p < n_pairs; ++p) {
+        if (pair_cell[p] < 0 || pair_cell[p] >= n_cells || pair_region[p] < 0 || pair_region[p] >= n_regions)
+            return fail(MELISSA_ERR_ARG, "test pair %lld: cell/region index out of range", (long long)p);
+        if (pair_ptr[p + 1] < pair_ptr[p]) return fail(MELISSA_ERR_ARG, "test pair_ptr must be non-decreasing");
+    }
+    const int D = n_basis + 1;
+    const int64_t nnz = pair_ptr[n_pairs];
+    // carve the fixed array: every piece starts on a 256-byte boundary
+    auto up = [](int64_t b) { return (b + 255) & ~int64_t(255); };
+    const int64_t sz_ptr = up((n_pairs + 1) * (int64_t)sizeof(int64_t)), sz_idx = up(n_pairs * (int64_t)sizeof(int32_t));
+    const int64_t sz_x = up(nnz * (int64_t)sizeof(double));
+    const int64_t sz_W = up((int64_t)n_regions * D * K * (int64_t)sizeof(double));
+    const int64_t sz_r = up((int64_t)n_cells * K * (int64_t)sizeof(double));
+    const int64_t need = sz_ptr + 2 * sz_idx + 2 * sz_x + sz_W + sz_r;
+    if (need > (int64_t)MELISSA_NOALLOC_SCRATCH_BYTES)
+        return fail(MELISSA_ERR_ARG,
+                    "melissa_impute_noalloc: this call needs %lld bytes of device staging but the fixed scratch "
+                    "array holds %lld; split the batch or use melissa_impute",
+                    (long long)need, (long long)MELISSA_NOALLOC_SCRATCH_BYTES);
+    unsigned char *base = nullptr;
+    int rc = noalloc_device_ptr(device, &base);
+    if (rc) return rc;
+    CU(cudaSetDevice(device));
+    unsigned char *cur = base;
+    int64_t *d_ptr = reinterpret_cast<int64_t *>(cur); cur += sz_ptr;
+    int32_t *d_cell = reinterpret_cast<int32_t *>(cur); cur += sz_idx;
+    int32_t *d_reg = reinterpret_cast<int32_t *>(cur); cur += sz_idx;
+    double *d_x = reinterpret_cast<double *>(cur); cur += sz_x;
+    double *d_pred = reinterpret_cast<double *>(cur); cur += sz_x;
+    double *d_W = reinterpret_cast<double *>(cur); cur += sz_W;
+    double *d_r = reinterpret_cast<double *>(cur);
+    // The array keeps whatever the previous call left in it.  Nothing here relies on
+    // zeros: each input piece is overwritten in full before the launch, and the
+    // kernel writes every pred[i], i < nnz, before it is copied out.
+    CU(cudaMemcpy(d_ptr, pair_ptr, (size_t)(n_pairs + 1) * sizeof(int64_t), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(d_cell, pair_cell, (size_t)n_pairs * sizeof(int32_t), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(d_reg, pair_region, (size_t)n_pairs * sizeof(int32_t), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(d_x, x, (size_t)nnz * sizeof(double), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(d_W, W, (size_t)n_regions * D * K * sizeof(double), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(d_r, r_nk, (size_t)n_cells * K * sizeof(double), cudaMemcpyHostToDevice));
+    BasisDev basis{};
+    basis.D = D; basis.gamma = gamma;
+    for (int j = 0; j < MAX_MUS; ++j) basis.mus[j] = j < n_basis ? mus[j] : 0.0;
+    int sm_count = 148;
+    cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device);
+    const int grid = grid_for(n_pairs, 128, sm_count, 16);
+    auto run = [&]() -> int {
+        DISPATCH_D(D, impute_kernel<DD><<<grid, 128>>>(d_ptr, d_cell, d_reg, d_x, d_W, d_r, d_pred, n_pairs,
+                                                      n_cells, n_regions, K, basis));
+        return MELISSA_OK;
+    };
+    if ((rc = run())) return rc;
+    CU(cudaGetLastError());
+    CU(cudaMemcpy(pred, d_pred, (size_t)nnz * sizeof(double), cudaMemcpyDeviceToHost));
     return MELISSA_OK;
 }
 
