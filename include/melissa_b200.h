@@ -89,6 +89,16 @@ int melissa_pack_device(int32_t n_cells, int32_t n_regions, int64_t n_pairs,
                         int32_t basis_kind, int32_t n_basis, const double *mus, double gamma,
                         int32_t device, int32_t allow_empty_regions, melissa_handle **out);
 
+/*
+ * Library-wide tuning knobs, read by the next melissa_pack*.  No counterpart in the
+ * reference.
+ *   "cell_block"  cells per block of the sliced layout (default 128)
+ *   "sliced"      -1 = use the sliced layout whenever the RBF centres are equally
+ *                 spaced (default), 0 = always the flat cell-major layout, 1 = require
+ *                 the sliced layout (pack fails if it cannot be used)
+ */
+int melissa_set_option(const char *key, int64_t value);
+
 /* Release every device and host resource behind the handle (NULL is a no-op). */
 int melissa_free(melissa_handle *h);
 

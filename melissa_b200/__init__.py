@@ -7,11 +7,11 @@ Public surface mirrors the reference's R functions for this path:
 libmelissa_b200.so (CUDA, sm_100a); there is no CPU fallback.
 """
 from .data import MelissaData, create_rbf_object, from_dict, from_nested, to_nested
-from .engine import Engine
+from .engine import Engine, set_option
 from .evaluate import (cluster_ari, eval_cluster_performance, eval_imputation_performance,
                        impute_test_met)
 from .vb import MelissaResult, finalize, melissa, melissa_inner, melissa_vb, shard_bounds, vb_loop
 
-__all__ = ["MelissaData", "create_rbf_object", "from_dict", "from_nested", "to_nested", "Engine",
+__all__ = ["MelissaData", "create_rbf_object", "from_dict", "from_nested", "to_nested", "Engine", "set_option",
            "cluster_ari", "eval_cluster_performance", "eval_imputation_performance", "impute_test_met",
            "MelissaResult", "finalize", "melissa", "melissa_inner", "melissa_vb", "shard_bounds", "vb_loop"]

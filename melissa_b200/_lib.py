@@ -22,6 +22,7 @@ SIGNATURES = {
                                c_i32, c_i32, C.POINTER(handle_t)]),
     "melissa_pack_device": (C.c_int, [c_i32, c_i32, c_i64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                       c_i32, c_i32, p_dbl, c_dbl, c_i32, c_i32, C.POINTER(handle_t)]),
+    "melissa_set_option": (C.c_int, [C.c_char_p, c_i64]),
     "melissa_free": (C.c_int, [handle_t]),
     "melissa_profile_enable": (C.c_int, [handle_t, c_i32]),
     "melissa_profile_read": (C.c_int, [handle_t, c_i32, p_dbl, p_i64]),

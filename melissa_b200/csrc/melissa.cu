@@ -26,6 +26,7 @@
 #include <cstring>
 #include <limits>
 #include <mutex>
+#include <thread>
 #include <string>
 #include <vector>
 
@@ -67,6 +68,10 @@ struct Scalars {
 
 }  // namespace
 
+namespace {
+struct Sliced;
+}
+
 struct melissa_handle {
     int device = 0;
     int N = 0, M = 0, D = 0, T = 0, R = 0;
@@ -100,6 +105,7 @@ struct melissa_handle {
     bool prof_on = false;
     std::vector<cudaEvent_t> prof_ev;      // start/stop pairs
     std::vector<int> prof_id;
+    Sliced *sl = nullptr;                  // v2 layout (sliced.cuh); null = v1 path
 };
 
 namespace {
@@ -588,6 +594,12 @@ __global__ void impute_kernel(const int64_t *__restrict__ pair_ptr, const int32_
     }
 }
 
+#include "sliced.cuh"
+
+// library-wide options (melissa_set_option)
+int g_opt_cell_block = 128;
+int g_opt_sliced = -1;   // -1 auto, 0 never, 1 require
+
 void prof_begin(melissa_handle *h, int id) {
     h->launches++;
     if (!h->prof_on) return;
@@ -679,10 +691,316 @@ int dev_alloc(Tp **p, int64_t n) {
     return MELISSA_OK;
 }
 
+
+// ---------------------------------------------------------------------------
+// v2 (sliced) host side: layout construction and launchers
+// ---------------------------------------------------------------------------
+struct SliceBuild {   // slices of a contiguous range of cell blocks, built by one host thread
+    std::vector<int32_t> slice_region, slice_len, slice_cb, lane_cell, lane_pair;
+    std::vector<int16_t> lane_len;
+    std::vector<int64_t> lane_src;
+};
+
+void build_slices_range(int cb_lo, int cb_hi, int Tn, int N, int M, const int64_t *cell_ptr,
+                        const int64_t *pair_ptr, const int32_t *pair_region, SliceBuild &out) {
+    std::vector<int32_t> cnt((size_t)M + 1), order;
+    std::vector<int64_t> tmp;
+    for (int cb = cb_lo; cb < cb_hi; ++cb) {
+        const int c0 = cb * Tn, c1 = std::min(N, c0 + Tn);
+        const int64_t p0 = cell_ptr[c0], p1 = cell_ptr[c1];
+        std::fill(cnt.begin(), cnt.end(), 0);
+        for (int64_t p = p0; p < p1; ++p) cnt[(size_t)pair_region[p] + 1]++;
+        for (int m = 0; m < M; ++m) cnt[(size_t)m + 1] += cnt[m];
+        order.resize((size_t)(p1 - p0));
+        {
+            std::vector<int32_t> cur(cnt.begin(), cnt.end() - 1);
+            for (int64_t p = p0; p < p1; ++p) order[(size_t)cur[pair_region[p]]++] = (int32_t)(p - p0);
+        }
+        // cell of a pair: pairs are cell-major, recover by walking cell_ptr
+        std::vector<int32_t> cell_of((size_t)(p1 - p0));
+        for (int c = c0; c < c1; ++c)
+            for (int64_t p = cell_ptr[c]; p < cell_ptr[c + 1]; ++p) cell_of[(size_t)(p - p0)] = c;
+        for (int m = 0; m < M; ++m) {
+            const int b = cnt[m], e = cnt[(size_t)m + 1];
+            if (b == e) continue;
+            // longest first; ties keep cell order
+            std::stable_sort(order.begin() + b, order.begin() + e, [&](int32_t u, int32_t v) {
+                return (pair_ptr[p0 + u + 1] - pair_ptr[p0 + u]) > (pair_ptr[p0 + v + 1] - pair_ptr[p0 + v]);
+            });
+            for (int q = b; q < e; q += 32) {
+                const int fill = std::min(32, e - q);
+                const int64_t pl = p0 + order[q];
+                out.slice_region.push_back(m);
+                out.slice_cb.push_back(cb);
+                out.slice_len.push_back((int32_t)(pair_ptr[pl + 1] - pair_ptr[pl]));
+                for (int l = 0; l < 32; ++l) {
+                    if (l < fill) {
+                        const int64_t p = p0 + order[q + l];
+                        out.lane_cell.push_back(cell_of[(size_t)(p - p0)]);
+                        out.lane_pair.push_back((int32_t)p);
+                        out.lane_len.push_back((int16_t)(pair_ptr[p + 1] - pair_ptr[p]));
+                        out.lane_src.push_back(pair_ptr[p]);
+                    } else {
+                        out.lane_cell.push_back(-1);
+                        out.lane_pair.push_back(-1);
+                        out.lane_len.push_back(0);
+                        out.lane_src.push_back(0);
+                    }
+                }
+            }
+        }
+    }
+}
+
+bool rbf_equally_spaced(const BasisDev &b) {
+    const int nb = b.D - 1;
+    if (nb <= 1) return true;
+    const double delta = b.mus[1] - b.mus[0];
+    if (!(delta > 0.0)) return false;
+    for (int j = 2; j < nb; ++j)
+        if (std::fabs((b.mus[j] - b.mus[0]) - j * delta) > 1e-12) return false;
+    return true;
+}
+
+void free_sliced(melissa_handle *h) {
+    Sliced *sl = h->sl;
+    if (!sl) return;
+    cudaFree(sl->x_sell); cudaFree(sl->ybits); cudaFree(sl->slice_xbase); cudaFree(sl->slice_ybase);
+    cudaFree(sl->slice_len); cudaFree(sl->slice_region); cudaFree(sl->lane_cell); cudaFree(sl->lane_len);
+    cudaFree(sl->item_begin); cudaFree(sl->item_cb); cudaFree(sl->cb_item_ptr); cudaFree(sl->reg_slice_ptr);
+    cudaFree(sl->reg_slice); cudaFree(sl->stats); cudaFree(sl->mills_tab); cudaFree(sl->rbf_tab);
+    cudaFree(sl->part); cudaFree(sl->lb_part);
+    delete sl;
+    h->sl = nullptr;
+}
+
+template <typename Tp>
+int upload(Tp **dst, const std::vector<Tp> &v) {
+    int rc = dev_alloc(dst, (int64_t)v.size());
+    if (rc) return rc;
+    if (!v.empty()) CU(cudaMemcpy(*dst, v.data(), v.size() * sizeof(Tp), cudaMemcpyHostToDevice));
+    return MELISSA_OK;
+}
+
+// Builds the sliced layout from the host index lists and the device-resident x / y.
+int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair_cell,
+                 const int32_t *pair_region) {
+    const int N = h->N, M = h->M;
+    const int64_t P = h->P;
+    Sliced *sl = new Sliced();
+    h->sl = sl;
+    sl->Tn = std::max(1, g_opt_cell_block);
+    const int Tn = sl->Tn;
+    sl->NB = (N + Tn - 1) / Tn;
+    for (int64_t p = 0; p < P; ++p)
+        if (pair_ptr[p + 1] - pair_ptr[p] > 32767)
+            return fail(MELISSA_ERR_ARG, "pair %lld has more than 32767 CpGs", (long long)p);
+    std::vector<int64_t> cell_ptr((size_t)N + 1, 0);
+    for (int64_t p = 0; p < P; ++p) cell_ptr[(size_t)pair_cell[p] + 1]++;
+    for (int n = 0; n < N; ++n) cell_ptr[(size_t)n + 1] += cell_ptr[n];
+    // ---- slices, built by a few host threads over ranges of cell blocks
+    int nthr = (int)std::min<int64_t>(std::max(1u, std::thread::hardware_concurrency()), 16);
+    nthr = std::max(1, std::min(nthr, sl->NB));
+    if (P < 200000) nthr = 1;
+    std::vector<SliceBuild> parts((size_t)nthr);
+    {
+        std::vector<std::thread> th;
+        for (int t = 0; t < nthr; ++t) {
+            const int lo = (int)((int64_t)sl->NB * t / nthr), hi = (int)((int64_t)sl->NB * (t + 1) / nthr);
+            th.emplace_back([&, t, lo, hi]() {
+                build_slices_range(lo, hi, Tn, N, M, cell_ptr.data(), pair_ptr, pair_region, parts[(size_t)t]);
+            });
+        }
+        for (auto &t : th) t.join();
+    }
+    SliceBuild all;
+    for (auto &pt : parts) {
+        all.slice_region.insert(all.slice_region.end(), pt.slice_region.begin(), pt.slice_region.end());
+        all.slice_len.insert(all.slice_len.end(), pt.slice_len.begin(), pt.slice_len.end());
+        all.slice_cb.insert(all.slice_cb.end(), pt.slice_cb.begin(), pt.slice_cb.end());
+        all.lane_cell.insert(all.lane_cell.end(), pt.lane_cell.begin(), pt.lane_cell.end());
+        all.lane_pair.insert(all.lane_pair.end(), pt.lane_pair.begin(), pt.lane_pair.end());
+        all.lane_len.insert(all.lane_len.end(), pt.lane_len.begin(), pt.lane_len.end());
+        all.lane_src.insert(all.lane_src.end(), pt.lane_src.begin(), pt.lane_src.end());
+        pt = SliceBuild();
+    }
+    const int64_t S = (int64_t)all.slice_region.size();
+    sl->S = S;
+    if (S >= (int64_t)std::numeric_limits<int32_t>::max()) return fail(MELISSA_ERR_ARG, "too many slices");
+    std::vector<int64_t> xbase((size_t)S), ybase((size_t)S);
+    int64_t xo = 0, yo = 0;
+    for (int64_t q = 0; q < S; ++q) {
+        xbase[(size_t)q] = xo;
+        ybase[(size_t)q] = yo;
+        xo += (int64_t)all.slice_len[(size_t)q] * 32;
+        yo += (int64_t)((all.slice_len[(size_t)q] + 31) / 32) * 32;
+    }
+    sl->x_len = xo;
+    sl->y_len = yo;
+    // ---- work items: runs of slices inside one cell block
+    // a CTA (up to 8 warps) should see >= 16 slices per warp so its prologue (tables, accumulators) amortises
+    const int64_t target_items = std::max<int64_t>(1, (int64_t)h->sm_count * 16);
+    const int64_t per_item = std::max<int64_t>(128, (S + target_items - 1) / target_items);
+    std::vector<int64_t> item_begin;
+    std::vector<int32_t> item_cb, cb_item_ptr((size_t)sl->NB + 1, 0);
+    {
+        int64_t q = 0;
+        for (int cb = 0; cb < sl->NB; ++cb) {
+            cb_item_ptr[(size_t)cb] = (int32_t)item_cb.size();
+            int64_t e = q;
+            while (e < S && all.slice_cb[(size_t)e] == cb) ++e;
+            for (int64_t b = q; b < e; b += per_item) {
+                item_begin.push_back(b);
+                item_cb.push_back(cb);
+            }
+            q = e;
+        }
+        cb_item_ptr[(size_t)sl->NB] = (int32_t)item_cb.size();
+        item_begin.push_back(S);
+    }
+    sl->n_items = (int64_t)item_cb.size();
+    // ---- region-major list of slices
+    std::vector<int64_t> reg_slice_ptr((size_t)M + 1, 0);
+    std::vector<int32_t> reg_slice((size_t)S);
+    for (int64_t q = 0; q < S; ++q) reg_slice_ptr[(size_t)all.slice_region[(size_t)q] + 1]++;
+    for (int m = 0; m < M; ++m) reg_slice_ptr[(size_t)m + 1] += reg_slice_ptr[m];
+    {
+        std::vector<int64_t> cur(reg_slice_ptr.begin(), reg_slice_ptr.end() - 1);
+        for (int64_t q = 0; q < S; ++q) reg_slice[(size_t)cur[all.slice_region[(size_t)q]]++] = (int32_t)q;
+    }
+    // ---- RBF table (host exp) and the Mills table (device erfcx)
+    const BasisDev &b = h->basis;
+    const int nb = b.D - 1;
+    RbfTab &rt = sl->rt;
+    std::vector<double2> rbf_tab;
+    if (nb >= 1) {
+        const double delta = nb >= 2 ? (b.mus[1] - b.mus[0]) : 1.0;
+        rt.mu1 = b.mus[0];
+        rt.s = delta / RBF_SUB;
+        rt.inv_s = 1.0 / rt.s;
+        rt.neg_gamma = -b.gamma;
+        rt.g2d = 2.0 * b.gamma * delta;
+        rt.q = std::exp(-b.gamma * delta * delta);
+        rt.q2 = rt.q * rt.q;
+        const int k_lo = (int)std::floor((-1.0 - rt.mu1) * rt.inv_s) - 2, k_hi = (int)std::ceil((1.0 - rt.mu1) * rt.inv_s) + 2;
+        rt.idx0 = -k_lo;
+        rt.n_entries = k_hi - k_lo + 1;
+        rbf_tab.resize((size_t)rt.n_entries);
+        for (int k = k_lo; k <= k_hi; ++k) {
+            const double u0 = (double)k * rt.s;
+            rbf_tab[(size_t)(k - k_lo)] = make_double2(std::exp(-b.gamma * u0 * u0), std::exp(rt.g2d * u0));
+        }
+    } else {
+        rt = RbfTab{};
+        rt.n_entries = 1;
+        rbf_tab.assign(1, make_double2(1.0, 1.0));
+    }
+    // ---- upload
+    int rc;
+    int64_t *d_src = nullptr;
+    if ((rc = upload(&sl->slice_xbase, xbase)) || (rc = upload(&sl->slice_ybase, ybase)) ||
+        (rc = upload(&sl->slice_len, all.slice_len)) || (rc = upload(&sl->slice_region, all.slice_region)) ||
+        (rc = upload(&sl->lane_cell, all.lane_cell)) || (rc = upload(&sl->lane_len, all.lane_len)) ||
+        (rc = upload(&sl->item_begin, item_begin)) || (rc = upload(&sl->item_cb, item_cb)) ||
+        (rc = upload(&sl->cb_item_ptr, cb_item_ptr)) || (rc = upload(&sl->reg_slice_ptr, reg_slice_ptr)) ||
+        (rc = upload(&sl->reg_slice, reg_slice)) || (rc = upload(&sl->rbf_tab, rbf_tab)) ||
+        (rc = upload(&d_src, all.lane_src)))
+        return rc;
+    if ((rc = dev_alloc(&sl->x_sell, sl->x_len)) || (rc = dev_alloc(&sl->ybits, sl->y_len)) ||
+        (rc = dev_alloc(&sl->stats, S * h->R * 32)) || (rc = dev_alloc(&sl->mills_tab, MILLS_N))) {
+        cudaFree(d_src);
+        return rc;
+    }
+    const int grid = (int)((S * 32 + 255) / 256);
+    sell_fill_kernel<<<grid, 256>>>(h->x, h->y, d_src, sl->lane_len, sl->slice_xbase, sl->slice_ybase, sl->slice_len,
+                                    sl->x_sell, sl->ybits, S);
+    {
+        auto run = [&]() -> int {
+            DISPATCH_D(h->D, hh_sliced_kernel<DD><<<grid, 256>>>(sl->x_sell, sl->slice_xbase, sl->lane_len, sl->stats,
+                                                                S, h->basis));
+            return MELISSA_OK;
+        };
+        if ((rc = run())) { cudaFree(d_src); return rc; }
+    }
+    mills_table_kernel<<<(MILLS_N + 255) / 256, 256>>>(sl->mills_tab);
+    h->launches += 3;
+    const cudaError_t e = cudaDeviceSynchronize();
+    cudaFree(d_src);
+    if (e != cudaSuccess) return fail(MELISSA_ERR_CUDA, "sliced layout build failed: %s", cudaGetErrorString(e));
+    sl->lane_pair = std::move(all.lane_pair);
+    sl->on = true;
+    return MELISSA_OK;
+}
+
+size_t sweep_v2_smem(const melissa_handle *h, int nw) {
+    const Sliced *sl = h->sl;
+    return (size_t)sl->rt.n_entries * sizeof(double2) +
+           ((size_t)MILLS_N + 1 + (size_t)sl->Tn * h->K * (1 + nw) + (size_t)nw * h->K * h->R) * sizeof(double);
+}
+
+int sweep_v2_warps(const melissa_handle *h) {
+    for (int nw : {8, 4, 2, 1})
+        if (sweep_v2_smem(h, nw) <= (nw >= 4 ? 100u * 1024 : 220u * 1024)) return nw;
+    for (int nw : {4, 2, 1})
+        if (sweep_v2_smem(h, nw) <= 220u * 1024) return nw;
+    return 0;
+}
+
+int launch_sweep_v2(melissa_handle *h, bool with_lb, bool uniform_r) {
+    Sliced *sl = h->sl;
+    const int nw = sweep_v2_warps(h);
+    if (nw == 0) return fail(MELISSA_ERR_ARG, "K = %d needs more shared memory than one SM has; lower the cell block", h->K);
+    const size_t smem = sweep_v2_smem(h, nw);
+    SweepV2Args a;
+    a.x_sell = sl->x_sell; a.ybits = sl->ybits; a.slice_xbase = sl->slice_xbase; a.slice_ybase = sl->slice_ybase;
+    a.slice_len = sl->slice_len; a.slice_region = sl->slice_region; a.lane_cell = sl->lane_cell; a.lane_len = sl->lane_len;
+    a.item_begin = sl->item_begin; a.item_cb = sl->item_cb; a.stats = sl->stats; a.U = h->U; a.r = h->r;
+    a.part = sl->part; a.lb_part = sl->lb_part; a.mills_tab = sl->mills_tab; a.rbf_tab = sl->rbf_tab; a.rt = sl->rt;
+    a.basis = h->basis; a.K = h->K; a.Tn = sl->Tn; a.N = h->N;
+    const int grid = (int)sl->n_items, block = 32 * nw;
+    prof_begin(h, MELISSA_KERNEL_SWEEP);
+#define SWEEP2(LB_, UNI_)                                                                                   \
+    DISPATCH_D(h->D, {                                                                                      \
+        auto kfn = sweep_v2_kernel<DD, LB_, UNI_>;                                                          \
+        CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));              \
+        kfn<<<grid, block, smem, h->stream>>>(a);                                                           \
+    })
+    if (with_lb && uniform_r) { SWEEP2(true, true) }
+    else if (with_lb) { SWEEP2(true, false) }
+    else if (uniform_r) { SWEEP2(false, true) }
+    else { SWEEP2(false, false) }
+#undef SWEEP2
+    prof_end(h);
+    CU(cudaGetLastError());
+    if (with_lb) {
+        lb_reduce_kernel<<<1, 256, 0, h->stream>>>(sl->lb_part, sl->n_items, h->lbbuf);
+        h->launches++;
+        CU(cudaGetLastError());
+    }
+    return MELISSA_OK;
+}
+
+int launch_contract_v2(melissa_handle *h) {
+    Sliced *sl = h->sl;
+    constexpr int JC = 5, KC = 4;
+    const int combos = ((h->R + JC - 1) / JC) * ((h->K + KC - 1) / KC);
+    const int block = 32 * std::min(8, combos);
+    prof_begin(h, MELISSA_KERNEL_CONTRACT);
+    contract_v2_kernel<JC, KC><<<h->M, block, 0, h->stream>>>(sl->reg_slice_ptr, sl->reg_slice, sl->lane_cell, sl->stats,
+                                                             h->r, h->red, h->K, h->R);
+    prof_end(h);
+    CU(cudaGetLastError());
+    return MELISSA_OK;
+}
+
 void free_fit(melissa_handle *h) {
     cudaFree(h->U); cudaFree(h->Spk); cudaFree(h->r); cudaFree(h->log_r); cudaFree(h->log_rho);
     cudaFree(h->red); cudaFree(h->lbbuf); cudaFree(h->scal_mem);
     h->U = h->Spk = h->r = h->log_r = h->log_rho = h->red = h->lbbuf = h->scal_mem = nullptr;
+    if (h->sl) {
+        cudaFree(h->sl->part); cudaFree(h->sl->lb_part);
+        h->sl->part = h->sl->lb_part = nullptr;
+    }
     h->begun = false;
 }
 
@@ -775,8 +1093,16 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
             if (reg_cnt[(size_t)m + 1] == 0)
                 return fail(MELISSA_ERR_ARG, "region %d is not covered by any cell", m);
     for (int32_t m = 0; m < n_regions; ++m) reg_cnt[(size_t)m + 1] += reg_cnt[m];
-    std::vector<int32_t> reg_pair((size_t)P), reg_cell((size_t)P);
-    {
+    BasisDev basis_chk{};
+    basis_chk.D = n_basis + 1;
+    for (int j = 0; j < n_basis && j < MAX_MUS; ++j) basis_chk.mus[j] = mus[j];
+    const bool use_sliced = g_opt_sliced != 0 && rbf_equally_spaced(basis_chk);
+    if (g_opt_sliced == 1 && !use_sliced)
+        return fail(MELISSA_ERR_ARG, "the sliced path needs equally spaced RBF centres");
+    std::vector<int32_t> reg_pair, reg_cell;
+    if (!use_sliced) {
+        reg_pair.resize((size_t)P);
+        reg_cell.resize((size_t)P);
         std::vector<int64_t> cursor(reg_cnt.begin(), reg_cnt.end() - 1);
         for (int64_t p = 0; p < P; ++p) {
             const int64_t q = cursor[pair_region[p]]++;
@@ -796,21 +1122,11 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
     if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) h->sm_count = prop.multiProcessorCount;
     int rc = MELISSA_OK;
     auto bail = [&](int code) { melissa_free(h); return code; };
-    if ((rc = dev_alloc(&h->pair_ptr, P + 1))) return bail(rc);
-    if ((rc = dev_alloc(&h->pair_cell, P))) return bail(rc);
-    if ((rc = dev_alloc(&h->pair_region, P))) return bail(rc);
-    if ((rc = dev_alloc(&h->x, nnz))) return bail(rc);
-    if ((rc = dev_alloc(&h->y, nnz))) return bail(rc);
-    if ((rc = dev_alloc(&h->reg_ptr, (int64_t)n_regions + 1))) return bail(rc);
-    if ((rc = dev_alloc(&h->reg_pair, P))) return bail(rc);
-    if ((rc = dev_alloc(&h->reg_cell, P))) return bail(rc);
-    if ((rc = dev_alloc(&h->stats, P * h->R))) return bail(rc);
 #define H2D(dst, src, n, Tp)                                                                          \
     if (cudaMemcpyAsync(dst, src, (size_t)(n) * sizeof(Tp), cudaMemcpyDefault, nullptr) != cudaSuccess)    \
         return bail(fail(MELISSA_ERR_CUDA, "copy of " #src " failed: %s", cudaGetErrorString(cudaGetLastError())))
-    H2D(h->pair_ptr, pair_ptr_in, P + 1, int64_t);
-    H2D(h->pair_cell, pair_cell_in, P, int32_t);
-    H2D(h->pair_region, pair_region_in, P, int32_t);
+    if ((rc = dev_alloc(&h->x, nnz))) return bail(rc);
+    if ((rc = dev_alloc(&h->y, nnz))) return bail(rc);
     H2D(h->x, x, nnz, double);
     H2D(h->y, y, nnz, uint8_t);
     if (on_device) {
@@ -822,11 +1138,25 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
         cudaFree(bad);
         if (bad_h) return bail(fail(MELISSA_ERR_ARG, "%llu methylation states are not 0/1", bad_h));
     }
-    H2D(h->reg_ptr, reg_cnt.data(), n_regions + 1, int64_t);
-    H2D(h->reg_pair, reg_pair.data(), P, int32_t);
-    H2D(h->reg_cell, reg_cell.data(), P, int32_t);
-#undef H2D
-    {
+    if (use_sliced) {
+        // v2: re-lay the observations into region slices, then drop the flat copies
+        if ((rc = build_sliced(h, pair_ptr, pair_cell, pair_region))) return bail(rc);
+        cudaFree(h->x); cudaFree(h->y);
+        h->x = nullptr; h->y = nullptr;
+    } else {
+        if ((rc = dev_alloc(&h->pair_ptr, P + 1))) return bail(rc);
+        if ((rc = dev_alloc(&h->pair_cell, P))) return bail(rc);
+        if ((rc = dev_alloc(&h->pair_region, P))) return bail(rc);
+        if ((rc = dev_alloc(&h->reg_ptr, (int64_t)n_regions + 1))) return bail(rc);
+        if ((rc = dev_alloc(&h->reg_pair, P))) return bail(rc);
+        if ((rc = dev_alloc(&h->reg_cell, P))) return bail(rc);
+        if ((rc = dev_alloc(&h->stats, P * h->R))) return bail(rc);
+        H2D(h->pair_ptr, pair_ptr_in, P + 1, int64_t);
+        H2D(h->pair_cell, pair_cell_in, P, int32_t);
+        H2D(h->pair_region, pair_region_in, P, int32_t);
+        H2D(h->reg_ptr, reg_cnt.data(), n_regions + 1, int64_t);
+        H2D(h->reg_pair, reg_pair.data(), P, int32_t);
+        H2D(h->reg_cell, reg_cell.data(), P, int32_t);
         const int grid = grid_for(P, 128, h->sm_count, 16);
         auto run = [&]() -> int {
             DISPATCH_D(h->D, hh_kernel<DD><<<grid, 128>>>(h->pair_ptr, h->x, h->stats, P, h->basis));
@@ -835,6 +1165,7 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
         if ((rc = run())) return bail(rc);
         h->launches++;
     }
+#undef H2D
     if (cudaDeviceSynchronize() != cudaSuccess)
         return bail(fail(MELISSA_ERR_CUDA, "pack failed: %s", cudaGetErrorString(cudaGetLastError())));
     *out = h;
@@ -855,6 +1186,21 @@ int melissa_pack_device(int32_t n_cells, int32_t n_regions, int64_t n_pairs, con
                         double gamma, int32_t device, int32_t allow_empty_regions, melissa_handle **out) {
     return pack_impl(n_cells, n_regions, n_pairs, pair_ptr, pair_cell, pair_region, x, y, basis_kind, n_basis, mus,
                      gamma, device, allow_empty_regions, true, out);
+}
+
+int melissa_set_option(const char *key, int64_t value) {
+    if (!key) return fail(MELISSA_ERR_ARG, "key is NULL");
+    if (!std::strcmp(key, "cell_block")) {
+        if (value < 1 || value > 4096) return fail(MELISSA_ERR_ARG, "cell_block must be in 1..4096");
+        g_opt_cell_block = (int)value;
+        return MELISSA_OK;
+    }
+    if (!std::strcmp(key, "sliced")) {
+        if (value < -1 || value > 1) return fail(MELISSA_ERR_ARG, "sliced must be -1 (auto), 0 or 1");
+        g_opt_sliced = (int)value;
+        return MELISSA_OK;
+    }
+    return fail(MELISSA_ERR_ARG, "unknown option '%s'", key);
 }
 
 int melissa_profile_enable(melissa_handle *h, int32_t on) {
@@ -890,6 +1236,7 @@ int melissa_free(melissa_handle *h) {
     cudaSetDevice(h->device);
     for (cudaEvent_t e : h->prof_ev) cudaEventDestroy(e);
     free_fit(h);
+    free_sliced(h);
     cudaFree(h->pair_ptr); cudaFree(h->pair_cell); cudaFree(h->pair_region); cudaFree(h->x);
     cudaFree(h->y); cudaFree(h->reg_ptr); cudaFree(h->reg_pair); cudaFree(h->reg_cell);
     cudaFree(h->stats);
@@ -953,8 +1300,14 @@ int melissa_vb_begin(melissa_handle *h, int32_t K, const double *w0, const doubl
     h->launches++;
     CU(cudaGetLastError());
     h->begun = true;
+    if (h->sl) {
+        if ((rc = dev_alloc(&h->sl->part, h->sl->n_items * h->sl->Tn * K))) return rc;
+        if ((rc = dev_alloc(&h->sl->lb_part, h->sl->n_items * 2))) return rc;
+        if (sweep_v2_warps(h) == 0)
+            return fail(MELISSA_ERR_ARG, "K = %d does not fit the sweep's shared memory at cell block %d", K, h->sl->Tn);
+    }
     // mu from rowMeans(w), E[z], E-step terms for i = 2  (R/melissa_vb.R:283-302)
-    return launch_sweep(h, false, true);
+    return h->sl ? launch_sweep_v2(h, false, true) : launch_sweep(h, false, true);
 }
 
 int melissa_vb_phase_a(melissa_handle *h) {
@@ -964,11 +1317,16 @@ int melissa_vb_phase_a(melissa_handle *h) {
     CU(cudaMemsetAsync(h->red, 0, (size_t)h->red_len * sizeof(double), h->stream));
     double *colsum = h->red + MK * h->R, *rlogr = colsum + h->K;
     prof_begin(h, MELISSA_KERNEL_RESP);
-    resp_kernel<<<(h->N + 127) / 128, 128, 0, h->stream>>>(h->log_rho, h->sc.elogpi, h->r, h->log_r, colsum,
-                                                          rlogr, h->sc.Eww_acc, h->sc.logdet_acc, h->N, h->K);
+    if (h->sl)
+        resp_v2_kernel<<<(h->N + 127) / 128, 128, 0, h->stream>>>(h->sl->part, h->sl->cb_item_ptr, h->sc.elogpi, h->r,
+                                                                 h->log_r, colsum, rlogr, h->sc.Eww_acc,
+                                                                 h->sc.logdet_acc, h->N, h->K, h->sl->Tn);
+    else
+        resp_kernel<<<(h->N + 127) / 128, 128, 0, h->stream>>>(h->log_rho, h->sc.elogpi, h->r, h->log_r, colsum,
+                                                              rlogr, h->sc.Eww_acc, h->sc.logdet_acc, h->N, h->K);
     prof_end(h);
     CU(cudaGetLastError());
-    return launch_contract(h);
+    return h->sl ? launch_contract_v2(h) : launch_contract(h);
 }
 
 int melissa_vb_phase_b(melissa_handle *h, int32_t with_lb) {
@@ -993,6 +1351,7 @@ int melissa_vb_phase_b(melissa_handle *h, int32_t with_lb) {
     scalars_kernel<<<1, 32, 0, h->stream>>>(h->sc, colsum, h->K, h->alpha_k, h->beta_0, (double)h->N_total, 0);
     prof_end(h);
     CU(cudaGetLastError());
+    if (h->sl) return launch_sweep_v2(h, with_lb != 0, false);
     if (with_lb) CU(cudaMemsetAsync(h->lbbuf, 0, 2 * sizeof(double), h->stream));
     return launch_sweep(h, with_lb != 0, false);
 }
@@ -1086,6 +1445,20 @@ int melissa_vb_fetch_HtEz(melissa_handle *h, double *out) {
     if (!out) return fail(MELISSA_ERR_ARG, "out is NULL");
     CU(cudaSetDevice(h->device));
     CU(cudaStreamSynchronize(h->stream));
+    if (h->sl) {
+        const Sliced *sl = h->sl;
+        const size_t row = (size_t)h->D * 32;
+        std::vector<double> buf((size_t)sl->S * row);
+        CU(cudaMemcpy2D(buf.data(), row * sizeof(double), sl->stats, (size_t)h->R * 32 * sizeof(double),
+                        row * sizeof(double), (size_t)sl->S, cudaMemcpyDeviceToHost));
+        for (int64_t q = 0; q < sl->S; ++q)
+            for (int l = 0; l < 32; ++l) {
+                const int32_t p = sl->lane_pair[(size_t)q * 32 + l];
+                if (p < 0) continue;
+                for (int d = 0; d < h->D; ++d) out[(size_t)p * h->D + d] = buf[(size_t)q * row + (size_t)d * 32 + l];
+            }
+        return MELISSA_OK;
+    }
     CU(cudaMemcpy2D(out, (size_t)h->D * sizeof(double), h->stats, (size_t)h->R * sizeof(double),
                     (size_t)h->D * sizeof(double), (size_t)h->P, cudaMemcpyDeviceToHost));
     return MELISSA_OK;

@@ -1,0 +1,470 @@
+// v2 data path: "region-sliced ELL".
+//
+// Cells are cut into blocks of Tn; inside a block, the cells that cover region m are
+// sorted by their CpG count and grouped 32 at a time into a SLICE.  A slice is one
+// warp's unit of work: lane l owns pair (cell_l, m); CpG i of every lane sits in one
+// 256-byte row x_sell[xbase + 32 i + l], so each load is coalesced and all lanes walk
+// their CpGs in lock-step with (almost) equal trip counts.  Because the region is
+// the same for the whole warp, the q(w) record U[m] is a broadcast operand, and the
+// per-pair record is stored component-major, stats[slice][j][lane], so both the sweep
+// (writes g, reads H^T H) and the contraction (reads everything) see 256-byte rows.
+//
+// Included from melissa.cu inside its anonymous namespace.
+#pragma once
+
+struct RbfTab {
+    double mu1, s, inv_s, neg_gamma, g2d, q, q2;
+    int n_entries, idx0;
+};
+
+constexpr int MILLS_SP = 128;                 // table points per unit of t
+constexpr int MILLS_HALF = 8 * MILLS_SP;      // t in [-8, 8]
+constexpr int MILLS_N = 2 * MILLS_HALF + 1;
+constexpr int RBF_SUB = 128;                  // table points per centre spacing
+constexpr double MAGIC = 6755399441055744.0;  // 1.5 * 2^52: (v + MAGIC) - MAGIC rounds v to an integer
+
+struct Sliced {
+    bool on = false;
+    int Tn = 128, NB = 0;
+    int64_t S = 0, n_items = 0, x_len = 0, y_len = 0;
+    double *x_sell = nullptr;
+    uint32_t *ybits = nullptr;
+    int64_t *slice_xbase = nullptr, *slice_ybase = nullptr;
+    int32_t *slice_len = nullptr, *slice_region = nullptr;
+    int32_t *lane_cell = nullptr;
+    int16_t *lane_len = nullptr;
+    int64_t *item_begin = nullptr;        // [n_items + 1] slice ranges
+    int32_t *item_cb = nullptr;           // [n_items]
+    int32_t *cb_item_ptr = nullptr;       // [NB + 1]
+    int64_t *reg_slice_ptr = nullptr;     // [M + 1]
+    int32_t *reg_slice = nullptr;         // [S]
+    double *stats = nullptr;              // [S][R][32]
+    double *mills_tab = nullptr;          // [MILLS_N]
+    double2 *rbf_tab = nullptr;           // [rt.n_entries] (E(u0), B(u0))
+    RbfTab rt{};
+    double *part = nullptr;               // [n_items][Tn][K]   (per fit)
+    double *lb_part = nullptr;            // [n_items][2]       (per fit)
+    std::vector<int32_t> lane_pair;       // host: original pair of (slice, lane), -1 = padding
+};
+
+// R(t0) = Phi(t0) / phi(t0) on the grid t0 = (i - MILLS_HALF) / MILLS_SP.
+__global__ void mills_table_kernel(double *tab) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= MILLS_N) return;
+    const double t0 = (double)(i - MILLS_HALF) / (double)MILLS_SP;
+    const double v = fabs(t0) * 0.70710678118654752440;
+    double R = 1.25331413731550025121 * erfcx(v);
+    if (t0 > 0.0) R = 2.50662827463100050242 * exp(0.5 * t0 * t0) - R;
+    tab[i] = R;
+}
+
+// E[z | z > 0], z ~ N(t, 1), from the table: R = Phi/phi satisfies R' = 1 + t R, so all
+// Taylor coefficients about a grid point follow from R(t0) alone:
+//   c_0 = R0, c_1 = 1 + t0 R0, c_{n+1} = (c_{n-1} + t0 c_n) / (n + 1).
+// Order 6 at spacing 1/128 is at the rounding floor (tools/proto checks).
+__device__ __forceinline__ double trunc_mean_tab(double t, const double *__restrict__ tab) {
+    if (!(fabs(t) < 7.99)) return trunc_mean(t);
+    const double v = fma(t, (double)MILLS_SP, MAGIC);
+    const int i = __double2loint(v);
+    const double t0 = (v - MAGIC) * (1.0 / MILLS_SP);
+    const double d = t - t0;
+    const double R0 = tab[i + MILLS_HALF];
+    const double c1 = fma(t0, R0, 1.0);
+    const double c2 = 0.5 * fma(t0, c1, R0);
+    const double c3 = (1.0 / 3.0) * fma(t0, c2, c1);
+    const double c4 = 0.25 * fma(t0, c3, c2);
+    const double c5 = 0.2 * fma(t0, c4, c3);
+    const double c6 = (1.0 / 6.0) * fma(t0, c5, c4);
+    double R = fma(d, c6, c5);
+    R = fma(d, R, c4);
+    R = fma(d, R, c3);
+    R = fma(d, R, c2);
+    R = fma(d, R, c1);
+    R = fma(d, R, R0);
+    return t + __drcp_rn(R);
+}
+
+// RBF row from the position, equally spaced centres mu_j = mu_1 + (j-1) Delta:
+//   h_1 = exp(-gamma u^2),  h_{j+1} = h_j * b * q^(2j-1),  u = x - mu_1,
+//   b = exp(2 gamma Delta u), q = exp(-gamma Delta^2).
+// exp(-gamma u^2) and b come from a table at u0 = k s (s = Delta / RBF_SUB) times short
+// series in the remainder d = u - u0 (|arguments| < 0.05).
+template <int D>
+__device__ __forceinline__ void eval_basis_tab(double x, const RbfTab &rt, const double2 *__restrict__ tab,
+                                               const BasisDev &basis, double (&h)[D]) {
+    h[0] = 1.0;
+    if (D == 1) return;
+    const double u = x - rt.mu1;
+    const double v = fma(u, rt.inv_s, MAGIC);
+    const int idx = __double2loint(v) + rt.idx0;
+    const double u0 = (v - MAGIC) * rt.s;
+    const double d = u - u0;
+    if ((unsigned)idx >= (unsigned)rt.n_entries) {           // x outside [-1, 1]: plain evaluation
+        eval_basis<D>(x, basis, h);
+        return;
+    }
+    const double2 eb = tab[idx];
+    const double w = (rt.neg_gamma * d) * fma(2.0, u0, d);   // -gamma (2 u0 d + d^2)
+    double c = fma(w, 1.0 / 5040, 1.0 / 720);
+    c = fma(w, c, 1.0 / 120);
+    c = fma(w, c, 1.0 / 24);
+    c = fma(w, c, 1.0 / 6);
+    c = fma(w, c, 0.5);
+    c = fma(w, c, 1.0);
+    c = fma(w, c, 1.0);
+    h[1] = eb.x * c;
+    if (D > 2) {
+        const double z = rt.g2d * d;
+        double e = fma(z, 1.0 / 720, 1.0 / 120);
+        e = fma(z, e, 1.0 / 24);
+        e = fma(z, e, 1.0 / 6);
+        e = fma(z, e, 0.5);
+        e = fma(z, e, 1.0);
+        e = fma(z, e, 1.0);
+        double bj = (eb.y * e) * rt.q;
+#pragma unroll
+        for (int j = 2; j < D; ++j) {
+            h[j] = h[j - 1] * bj;
+            bj *= rt.q2;
+        }
+    }
+}
+
+// Re-lay x / y into slices.  One thread per (slice, lane).
+__global__ void sell_fill_kernel(const double *__restrict__ x, const uint8_t *__restrict__ y,
+                                 const int64_t *__restrict__ lane_src, const int16_t *__restrict__ lane_len,
+                                 const int64_t *__restrict__ slice_xbase, const int64_t *__restrict__ slice_ybase,
+                                 const int32_t *__restrict__ slice_len, double *__restrict__ x_sell,
+                                 uint32_t *__restrict__ ybits, int64_t S) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= S * 32) return;
+    const int64_t s = t >> 5;
+    const int lane = (int)(t & 31);
+    const int L = slice_len[s], len = lane_len[t];
+    const int64_t src = lane_src[t], xb = slice_xbase[s], yb = slice_ybase[s];
+    uint32_t word = 0;
+    for (int i = 0; i < L; ++i) {
+        double xv = 0.0;
+        if (i < len) {
+            xv = x[src + i];
+            word |= (uint32_t)(y[src + i] != 0) << (i & 31);
+        }
+        x_sell[xb + (int64_t)i * 32 + lane] = xv;
+        if ((i & 31) == 31 || i == L - 1) {
+            ybits[yb + (int64_t)(i >> 5) * 32 + lane] = word;
+            word = 0;
+        }
+    }
+}
+
+// H^T H per pair into stats[slice][D + t][lane]; g rows zeroed.  One thread per (slice, lane).
+template <int D>
+__global__ void hh_sliced_kernel(const double *__restrict__ x_sell, const int64_t *__restrict__ slice_xbase,
+                                 const int16_t *__restrict__ lane_len, double *__restrict__ stats, int64_t S,
+                                 BasisDev basis) {
+    constexpr int T = D * (D + 1) / 2, R = D + T;
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= S * 32) return;
+    const int64_t s = t >> 5;
+    const int lane = (int)(t & 31);
+    const int len = lane_len[t];
+    const int64_t xb = slice_xbase[s];
+    double hh[T];
+#pragma unroll
+    for (int q = 0; q < T; ++q) hh[q] = 0.0;
+    for (int i = 0; i < len; ++i) {
+        double h[D];
+        eval_basis<D>(x_sell[xb + (int64_t)i * 32 + lane], basis, h);
+        int q = 0;
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+#pragma unroll
+            for (int c = a; c < D; ++c) hh[q++] += h[a] * h[c];
+    }
+    double *rec = stats + s * R * 32 + lane;
+#pragma unroll
+    for (int d = 0; d < D; ++d) rec[d * 32] = 0.0;
+#pragma unroll
+    for (int q = 0; q < T; ++q) rec[(D + q) * 32] = hh[q];
+}
+
+struct SweepV2Args {
+    const double *x_sell;
+    const uint32_t *ybits;
+    const int64_t *slice_xbase, *slice_ybase;
+    const int32_t *slice_len, *slice_region, *lane_cell;
+    const int16_t *lane_len;
+    const int64_t *item_begin;
+    const int32_t *item_cb;
+    double *stats;
+    const double *U, *r;
+    double *part, *lb_part;
+    const double *mills_tab;
+    const double2 *rbf_tab;
+    RbfTab rt;
+    BasisDev basis;
+    int K, Tn, N;
+};
+
+// The per-CpG sweep on slices (R/melissa_vb.R:418-435 refresh + the next iteration's
+// E-step terms :322-327 + lb_pz_qz :469-473 when WITH_LB).  One CTA per work item (a
+// run of slices of one cell block), one warp per slice.
+template <int D, bool WITH_LB, bool UNIFORM_R>
+__global__ void __launch_bounds__(256, 2) sweep_v2_kernel(SweepV2Args a) {
+    constexpr int T = D * (D + 1) / 2, R = D + T;
+    constexpr int XU = 4;                       // CpG rows fetched per group (prefetch distance)
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ unsigned long long s_next;       // next unclaimed slice of this work item
+    const int K = a.K, Tn = a.Tn;
+    const int nw = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // shared: rbf table | mills table | r block | per-warp U staging | per-warp accumulators
+    double2 *s_rbf = reinterpret_cast<double2 *>(smem_raw);
+    double *s_mills = reinterpret_cast<double *>(s_rbf + a.rt.n_entries);
+    double *s_r = s_mills + MILLS_N + 1;
+    double *s_u = s_r + Tn * K;
+    double *s_acc = s_u + nw * K * R;
+    const int item = blockIdx.x;
+    const int cb = a.item_cb[item];
+    const int cell0 = cb * Tn;
+    const int64_t s_begin = a.item_begin[item], s_end = a.item_begin[item + 1];
+    if (threadIdx.x == 0) s_next = (unsigned long long)s_begin;
+    for (int i = threadIdx.x; i < a.rt.n_entries; i += blockDim.x) s_rbf[i] = a.rbf_tab[i];
+    for (int i = threadIdx.x; i < MILLS_N; i += blockDim.x) s_mills[i] = a.mills_tab[i];
+    const double inv_K = 1.0 / (double)K;
+    for (int i = threadIdx.x; i < Tn * K; i += blockDim.x) {
+        const int n = cell0 + i / K;
+        s_r[i] = UNIFORM_R ? inv_K : (n < a.N ? a.r[(int64_t)cell0 * K + i] : 0.0);
+    }
+    for (int i = threadIdx.x; i < nw * Tn * K; i += blockDim.x) s_acc[i] = 0.0;
+    __syncthreads();
+    double *my_u = s_u + warp * K * R;
+    double *my_acc = s_acc + warp * Tn * K;
+    double lb_local = 0.0, wrong_side = 0.0;
+    for (;;) {
+        // slices differ in length (longest pairs first inside a region), so warps take them on demand
+        unsigned long long claimed = 0;
+        if (lane == 0) claimed = atomicAdd(&s_next, 1ull);
+        const int64_t s = (int64_t)__shfl_sync(0xffffffffu, claimed, 0);
+        if (s >= s_end) break;
+        const int m = a.slice_region[s];
+        const int L = a.slice_len[s];
+        const int64_t xb = a.slice_xbase[s], yb = a.slice_ybase[s];
+        const int cell = a.lane_cell[s * 32 + lane];
+        const int len = a.lane_len[s * 32 + lane];
+        const bool valid = cell >= 0;
+        const int nl = valid ? cell - cell0 : 0;
+        const double *xrow = a.x_sell + xb + lane;
+        double xa[XU];
+#pragma unroll
+        for (int u = 0; u < XU; ++u) xa[u] = u < L ? xrow[u * 32] : 0.0;
+        uint32_t yw = a.ybits[yb + lane];
+        double *rec = a.stats + s * (R * 32) + lane;
+        double hh[T];
+#pragma unroll
+        for (int q = 0; q < T; ++q) hh[q] = rec[(D + q) * 32];
+        __syncwarp();
+        for (int i = lane; i < K * R; i += 32) my_u[i] = a.U[(int64_t)m * K * R + i];
+        __syncwarp();
+        // -1/2 tr(H^T H (m m^T + S)) needs no E[z]: do it while the first CpG rows are in flight
+        double wbar[D];
+#pragma unroll
+        for (int d = 0; d < D; ++d) wbar[d] = 0.0;
+        for (int k = 0; k < K; ++k) {
+            const double *u = my_u + k * R;
+            const double rk = s_r[nl * K + k];
+            double trc = 0.0;
+#pragma unroll
+            for (int q = 0; q < T; ++q) trc = fma(u[D + q], hh[q], trc);
+#pragma unroll
+            for (int d = 0; d < D; ++d) wbar[d] = fma(rk, u[d], wbar[d]);
+            if (valid) {
+                my_acc[nl * K + k] += trc;                 // lanes of one slice are distinct cells
+                if (WITH_LB) lb_local = fma(rk, trc, lb_local);
+            }
+        }
+        double g[D];
+#pragma unroll
+        for (int d = 0; d < D; ++d) g[d] = 0.0;
+        for (int i0 = 0; i0 < L; i0 += XU) {
+            double xnext[XU];
+#pragma unroll
+            for (int u = 0; u < XU; ++u) xnext[u] = (i0 + XU + u < L) ? xrow[(int64_t)(i0 + XU + u) * 32] : 0.0;
+            uint32_t ywn = yw;
+            if (((i0 + XU) & 31) == 0 && i0 + XU < L) ywn = a.ybits[yb + (int64_t)((i0 + XU) >> 5) * 32 + lane];
+#pragma unroll
+            for (int u = 0; u < XU; ++u) {
+                const int i = i0 + u;
+                if (i < L) {
+                    const bool yi = (yw >> (i & 31)) & 1u;
+                    double h[D];
+                    eval_basis_tab<D>(xa[u], a.rt, s_rbf, a.basis, h);
+                    double mu = wbar[0];
+#pragma unroll
+                    for (int d = 1; d < D; ++d) mu = fma(h[d], wbar[d], mu);
+                    const double t = yi ? mu : -mu;
+                    const double G = trunc_mean_tab(t, s_mills);
+                    double Ez = yi ? G : -G;
+                    if (i >= len) Ez = 0.0;
+                    g[0] += Ez;
+#pragma unroll
+                    for (int d = 1; d < D; ++d) g[d] = fma(h[d], Ez, g[d]);
+                    if (WITH_LB) {
+                        if (i < len) {
+                            lb_local += 0.5 * mu * mu + loglik_term(mu, yi);
+                            if (t < -5.0) wrong_side += 1.0;
+                        }
+                    }
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < XU; ++u) xa[u] = xnext[u];
+            yw = ywn;
+        }
+#pragma unroll
+        for (int d = 0; d < D; ++d) rec[d * 32] = g[d];
+        if (valid) {
+            for (int k = 0; k < K; ++k) {
+                const double *u = my_u + k * R;
+                double lin = 0.0;
+#pragma unroll
+                for (int d = 0; d < D; ++d) lin = fma(u[d], g[d], lin);
+                my_acc[nl * K + k] += lin;
+            }
+        }
+    }
+    __syncthreads();
+    double *out = a.part + (int64_t)item * Tn * K;
+    for (int i = threadIdx.x; i < Tn * K; i += blockDim.x) {
+        double v = 0.0;
+        for (int w = 0; w < nw; ++w) v += s_acc[w * Tn * K + i];
+        out[i] = v;
+    }
+    if (WITH_LB) {
+        __shared__ double red_smem[32];
+        double v = block_sum(lb_local, red_smem);
+        if (threadIdx.x == 0) a.lb_part[2 * item] = v;
+        v = block_sum(wrong_side, red_smem);
+        if (threadIdx.x == 0) a.lb_part[2 * item + 1] = v;
+    }
+}
+
+// Sum the per-item lower-bound partials in a fixed order.
+__global__ void lb_reduce_kernel(const double *__restrict__ lb_part, int64_t n_items, double *__restrict__ lbbuf) {
+    __shared__ double red_smem[32];
+    double a = 0.0, b = 0.0;
+    for (int64_t i = threadIdx.x; i < n_items; i += blockDim.x) {
+        a += lb_part[2 * i];
+        b += lb_part[2 * i + 1];
+    }
+    a = block_sum(a, red_smem);
+    b = block_sum(b, red_smem);
+    if (threadIdx.x == 0) {
+        lbbuf[0] = a;
+        lbbuf[1] = b;
+    }
+}
+
+// Responsibilities from the per-item E-step partials (v2 twin of resp_kernel).
+__global__ void __launch_bounds__(128)
+resp_v2_kernel(const double *__restrict__ part, const int32_t *__restrict__ cb_item_ptr,
+               const double *__restrict__ elogpi, double *__restrict__ r, double *__restrict__ log_r,
+               double *__restrict__ colsum, double *__restrict__ rlogr, double *__restrict__ Eww_acc,
+               double *__restrict__ logdet_acc, int N, int K, int Tn) {
+    __shared__ double red_smem[32];
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        *logdet_acc = 0.0;
+        for (int k = 0; k < K; ++k) Eww_acc[k] = 0.0;
+    }
+    double lse = 0.0, rl = 0.0;
+    const int cb = n < N ? n / Tn : 0, nl = n < N ? n % Tn : 0;
+    const int i0 = n < N ? cb_item_ptr[cb] : 0, i1 = n < N ? cb_item_ptr[cb + 1] : 0;
+    if (n < N) {
+        double mx = -INFINITY;
+        for (int k = 0; k < K; ++k) {
+            double v = 0.0;
+            for (int it = i0; it < i1; ++it) v += part[((int64_t)it * Tn + nl) * K + k];
+            v += elogpi[k];
+            log_r[(int64_t)n * K + k] = v;                      // log rho for now
+            mx = fmax(mx, v);
+        }
+        double s = 0.0;
+        for (int k = 0; k < K; ++k) s += exp(log_r[(int64_t)n * K + k] - mx);
+        lse = log(s) + mx;                                      // R/utils.R:16-20
+    }
+    for (int k = 0; k < K; ++k) {
+        double rk = 0.0;
+        if (n < N) {
+            const double lr = log_r[(int64_t)n * K + k] - lse;
+            rk = exp(lr);
+            log_r[(int64_t)n * K + k] = lr;
+            r[(int64_t)n * K + k] = rk;
+            rl += rk * lr;
+        }
+        const double s = block_sum(rk, red_smem);
+        if (threadIdx.x == 0) atomicAdd(&colsum[k], s);
+    }
+    const double s = block_sum(rl, red_smem);
+    if (threadIdx.x == 0) atomicAdd(rlogr, s);
+}
+
+// Contraction on slices: acc[m,k,j] = sum over the region's slices and lanes of
+// r[cell,k] * stats[slice][j][lane]  (R/melissa_vb.R:368-373 sums).  One CTA per region;
+// warp w takes the (component chunk, cluster chunk) combinations w, w + nw, ...; lanes
+// are pairs, JC x KC accumulators per lane, one butterfly at the end.  The slice ids of
+// the next 32 slices are fetched with one coalesced load and handed round by shuffle,
+// and two slices are in flight per loop trip, so the dependent index -> cell -> r loads
+// of one slice overlap the row loads of the other.
+template <int JC, int KC>
+__global__ void __launch_bounds__(256)
+contract_v2_kernel(const int64_t *__restrict__ reg_slice_ptr, const int32_t *__restrict__ reg_slice,
+                   const int32_t *__restrict__ lane_cell, const double *__restrict__ stats,
+                   const double *__restrict__ r, double *__restrict__ acc_out, int K, int R) {
+    const int m = blockIdx.x;
+    const int nw = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t q0 = reg_slice_ptr[m], q1 = reg_slice_ptr[m + 1];
+    const int njc = (R + JC - 1) / JC, nkc = (K + KC - 1) / KC;
+    for (int combo = warp; combo < njc * nkc; combo += nw) {
+        const int j0 = (combo % njc) * JC, k0 = (combo / njc) * KC;
+        double acc[JC][KC];
+#pragma unroll
+        for (int j = 0; j < JC; ++j)
+#pragma unroll
+            for (int c = 0; c < KC; ++c) acc[j][c] = 0.0;
+        for (int64_t base = q0; base < q1; base += 32) {
+            const int cnt = (int)min((int64_t)32, q1 - base);
+            const int my_s = lane < cnt ? reg_slice[base + lane] : 0;
+            for (int it = 0; it < cnt; it += 2) {
+                const int64_t sa = __shfl_sync(0xffffffffu, my_s, it);
+                const bool has_b = it + 1 < cnt;
+                const int64_t sb = __shfl_sync(0xffffffffu, my_s, has_b ? it + 1 : it);
+                const int cell_a = lane_cell[sa * 32 + lane];
+                const int cell_b = has_b ? lane_cell[sb * 32 + lane] : -1;
+                const double *rec_a = stats + sa * ((int64_t)R * 32) + lane;
+                const double *rec_b = stats + sb * ((int64_t)R * 32) + lane;
+                double va[JC], vb[JC], ra[KC], rb[KC];
+#pragma unroll
+                for (int j = 0; j < JC; ++j) {
+                    va[j] = (j0 + j < R) ? rec_a[(j0 + j) * 32] : 0.0;
+                    vb[j] = (has_b && j0 + j < R) ? rec_b[(j0 + j) * 32] : 0.0;
+                }
+#pragma unroll
+                for (int c = 0; c < KC; ++c) {
+                    ra[c] = (cell_a >= 0 && k0 + c < K) ? r[(int64_t)cell_a * K + k0 + c] : 0.0;
+                    rb[c] = (cell_b >= 0 && k0 + c < K) ? r[(int64_t)cell_b * K + k0 + c] : 0.0;
+                }
+#pragma unroll
+                for (int j = 0; j < JC; ++j)
+#pragma unroll
+                    for (int c = 0; c < KC; ++c) acc[j][c] = fma(ra[c], va[j], fma(rb[c], vb[j], acc[j][c]));
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < JC; ++j)
+#pragma unroll
+            for (int c = 0; c < KC; ++c) {
+                const double v = warp_sum(acc[j][c]);
+                if (lane == 0 && j0 + j < R && k0 + c < K) acc_out[((int64_t)m * K + k0 + c) * R + j0 + j] = v;
+            }
+    }
+}

@@ -10,6 +10,12 @@ from . import _lib
 from .data import MelissaData
 
 
+def set_option(key: str, value: int):
+    """Library-wide knob for the next pack: "cell_block" (cells per block of the sliced
+    layout, default 128) or "sliced" (-1 auto, 0 flat layout, 1 require sliced)."""
+    _lib.check(_lib.load().melissa_set_option(key.encode(), int(value)))
+
+
 class _DeviceBuffer:
     """Exposes a raw device pointer through __cuda_array_interface__ so torch can
     alias it (used only to hand the reduction buffers to torch.distributed)."""

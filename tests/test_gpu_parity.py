@@ -19,6 +19,21 @@ pytestmark = pytest.mark.gpu
 LB_RTOL = 1e-9
 
 
+@pytest.fixture(autouse=True, params=["sliced-block128", "sliced-block8", "flat"])
+def layout(request):
+    """Every parity test runs on the sliced layout (default cell block and a tiny one, so
+    that several cell blocks and work items are exercised on small data) and on the flat
+    cell-major layout."""
+    if request.param == "flat":
+        mb.set_option("sliced", 0)
+    else:
+        mb.set_option("sliced", 1)
+        mb.set_option("cell_block", int(request.param.split("block")[1]))
+    yield request.param
+    mb.set_option("sliced", -1)
+    mb.set_option("cell_block", 128)
+
+
 def _engine(d, basis, **kw):
     return mb.Engine(mb.from_dict(d), basis, **kw)
 

@@ -28,9 +28,14 @@ for i in range(10):
     e0.record(); eng.phase_a(); e1.record(); eng.phase_b(i == 9); e2.record()
     torch.cuda.synchronize()
     ta.append(e0.elapsed_time(e1)); (tl if i == 9 else tb).append(e1.elapsed_time(e2))
+eng.profile(True)
+for i in range(10):
+    eng.phase_a(); eng.phase_b(False)
+prof = {k: round(v[0] / max(1, v[1]), 4) for k, v in eng.profile_read().items()}
+eng.profile(False)
 lb = eng.lower_bound()
 res = eng.fetch()
 print(json.dumps(dict(N=N, M=M, K=K, P=d.P, nnz=d.nnz, gen_s=round(t_gen, 2), pack_s=round(t_pack, 2),
                       phase_a_ms=float(np.median(ta)), phase_b_ms=float(np.median(tb)), phase_b_lb_ms=tl[0],
-                      pairs_per_s=d.P / ((np.median(ta) + np.median(tb)) * 1e-3), lb=lb,
+                      pairs_per_s=d.P / ((np.median(ta) + np.median(tb)) * 1e-3), lb=lb, kernels_ms=prof,
                       ari=mb.cluster_ari(tr["C_true"], res["r_nk"]))))
