@@ -963,6 +963,7 @@ int launch_sweep_v2(melissa_handle *h, bool with_lb, bool uniform_r) {
     DISPATCH_D(h->D, {                                                                                      \
         auto kfn = sweep_v2_kernel<DD, LB_, UNI_>;                                                          \
         CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));              \
+        CU(cudaFuncSetAttribute(kfn, cudaFuncAttributePreferredSharedMemoryCarveout, 100));                 \
         kfn<<<grid, block, smem, h->stream>>>(a);                                                           \
     })
     if (with_lb && uniform_r) { SWEEP2(true, true) }

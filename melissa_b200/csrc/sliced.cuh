@@ -20,6 +20,9 @@ struct RbfTab {
 constexpr int MILLS_SP = 128;                 // table points per unit of t
 constexpr int MILLS_HALF = 8 * MILLS_SP;      // t in [-8, 8]
 constexpr int MILLS_N = 2 * MILLS_HALF + 1;
+#ifndef SWEEP_XU
+#define SWEEP_XU 4
+#endif
 constexpr int RBF_SUB = 128;                  // table points per centre spacing
 constexpr double MAGIC = 6755399441055744.0;  // 1.5 * 2^52: (v + MAGIC) - MAGIC rounds v to an integer
 
@@ -130,6 +133,72 @@ __device__ __forceinline__ void eval_basis_tab(double x, const RbfTab &rt, const
     }
 }
 
+// Branch-free twins of the two table functions for the sweep's inner loop: the table
+// index is clamped instead of tested, and the (never expected) out-of-range case is
+// reported through the return value so the caller can redo that CpG on the slow path.
+// Straight-line code lets the scheduler interleave the CpGs of one prefetch group.
+template <int D>
+__device__ __forceinline__ bool eval_basis_fast(double x, const RbfTab &rt, const double2 *__restrict__ tab,
+                                                double (&h)[D]) {
+    h[0] = 1.0;
+    if (D == 1) return false;
+    const double u = x - rt.mu1;
+    const double v = fma(u, rt.inv_s, MAGIC);
+    int idx = __double2loint(v) + rt.idx0;
+    const bool bad = (unsigned)idx >= (unsigned)rt.n_entries;
+    idx = min(max(idx, 0), rt.n_entries - 1);
+    const double u0 = (v - MAGIC) * rt.s;
+    const double d = u - u0;
+    const double2 eb = tab[idx];
+    const double w = (rt.neg_gamma * d) * fma(2.0, u0, d);
+    double c = fma(w, 1.0 / 5040, 1.0 / 720);
+    c = fma(w, c, 1.0 / 120);
+    c = fma(w, c, 1.0 / 24);
+    c = fma(w, c, 1.0 / 6);
+    c = fma(w, c, 0.5);
+    c = fma(w, c, 1.0);
+    c = fma(w, c, 1.0);
+    h[1] = eb.x * c;
+    if (D > 2) {
+        const double z = rt.g2d * d;
+        double e = fma(z, 1.0 / 720, 1.0 / 120);
+        e = fma(z, e, 1.0 / 24);
+        e = fma(z, e, 1.0 / 6);
+        e = fma(z, e, 0.5);
+        e = fma(z, e, 1.0);
+        e = fma(z, e, 1.0);
+        double bj = (eb.y * e) * rt.q;
+#pragma unroll
+        for (int j = 2; j < D; ++j) {
+            h[j] = h[j - 1] * bj;
+            bj *= rt.q2;
+        }
+    }
+    return bad;
+}
+
+__device__ __forceinline__ double trunc_mean_fast(double t, const double *__restrict__ tab, bool &bad) {
+    bad = !(fabs(t) < 7.99);
+    const double v = fma(t, (double)MILLS_SP, MAGIC);
+    const int i = min(max(__double2loint(v), -MILLS_HALF), MILLS_HALF);
+    const double t0 = (v - MAGIC) * (1.0 / MILLS_SP);
+    const double d = t - t0;
+    const double R0 = tab[i + MILLS_HALF];
+    const double c1 = fma(t0, R0, 1.0);
+    const double c2 = 0.5 * fma(t0, c1, R0);
+    const double c3 = (1.0 / 3.0) * fma(t0, c2, c1);
+    const double c4 = 0.25 * fma(t0, c3, c2);
+    const double c5 = 0.2 * fma(t0, c4, c3);
+    const double c6 = (1.0 / 6.0) * fma(t0, c5, c4);
+    double R = fma(d, c6, c5);
+    R = fma(d, R, c4);
+    R = fma(d, R, c3);
+    R = fma(d, R, c2);
+    R = fma(d, R, c1);
+    R = fma(d, R, R0);
+    return t + __drcp_rn(R);
+}
+
 // Re-lay x / y into slices.  One thread per (slice, lane).
 __global__ void sell_fill_kernel(const double *__restrict__ x, const uint8_t *__restrict__ y,
                                  const int64_t *__restrict__ lane_src, const int16_t *__restrict__ lane_len,
@@ -212,7 +281,7 @@ struct SweepV2Args {
 template <int D, bool WITH_LB, bool UNIFORM_R>
 __global__ void __launch_bounds__(256, 2) sweep_v2_kernel(SweepV2Args a) {
     constexpr int T = D * (D + 1) / 2, R = D + T;
-    constexpr int XU = 4;                       // CpG rows fetched per group (prefetch distance)
+    constexpr int XU = SWEEP_XU;                // CpG rows fetched per group (prefetch distance, ILP)
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ unsigned long long s_next;       // next unclaimed slice of this work item
     const int K = a.K, Tn = a.Tn;
@@ -285,6 +354,8 @@ __global__ void __launch_bounds__(256, 2) sweep_v2_kernel(SweepV2Args a) {
         double g[D];
 #pragma unroll
         for (int d = 0; d < D; ++d) g[d] = 0.0;
+        // Rows beyond L read as x = 0 and rows beyond a lane's own length are masked to
+        // E[z] = 0, so every group runs all XU rows with no trip-count test inside.
         for (int i0 = 0; i0 < L; i0 += XU) {
             double xnext[XU];
 #pragma unroll
@@ -294,25 +365,35 @@ __global__ void __launch_bounds__(256, 2) sweep_v2_kernel(SweepV2Args a) {
 #pragma unroll
             for (int u = 0; u < XU; ++u) {
                 const int i = i0 + u;
-                if (i < L) {
-                    const bool yi = (yw >> (i & 31)) & 1u;
-                    double h[D];
-                    eval_basis_tab<D>(xa[u], a.rt, s_rbf, a.basis, h);
-                    double mu = wbar[0];
+                const uint32_t ybit = (yw >> (i & 31)) & 1u;
+                const uint32_t sflip = (ybit ^ 1u) << 31;             // s = +1 for y = 1, -1 for y = 0
+                const uint32_t live = i < len ? 0xffffffffu : 0u;
+                double h[D];
+                bool bad = eval_basis_fast<D>(xa[u], a.rt, s_rbf, h);
+                double mu = wbar[0];
 #pragma unroll
-                    for (int d = 1; d < D; ++d) mu = fma(h[d], wbar[d], mu);
-                    const double t = yi ? mu : -mu;
-                    const double G = trunc_mean_tab(t, s_mills);
-                    double Ez = yi ? G : -G;
-                    if (i >= len) Ez = 0.0;
-                    g[0] += Ez;
+                for (int d = 1; d < D; ++d) mu = fma(h[d], wbar[d], mu);
+                double t = __hiloint2double(__double2hiint(mu) ^ sflip, __double2loint(mu));
+                bool bad_t;
+                double G = trunc_mean_fast(t, s_mills, bad_t);
+                if (__any_sync(0xffffffffu, (bad || bad_t) && live)) {     // never taken on sane data
+                    if (bad) {
+                        eval_basis<D>(xa[u], a.basis, h);
+                        mu = wbar[0];
 #pragma unroll
-                    for (int d = 1; d < D; ++d) g[d] = fma(h[d], Ez, g[d]);
-                    if (WITH_LB) {
-                        if (i < len) {
-                            lb_local += 0.5 * mu * mu + loglik_term(mu, yi);
-                            if (t < -5.0) wrong_side += 1.0;
-                        }
+                        for (int d = 1; d < D; ++d) mu = fma(h[d], wbar[d], mu);
+                        t = ybit ? mu : -mu;
+                    }
+                    if (bad || bad_t) G = trunc_mean(t);
+                }
+                const double Ez = __hiloint2double((__double2hiint(G) ^ sflip) & live, __double2loint(G) & live);
+                g[0] += Ez;
+#pragma unroll
+                for (int d = 1; d < D; ++d) g[d] = fma(h[d], Ez, g[d]);
+                if (WITH_LB) {
+                    if (live) {
+                        lb_local += 0.5 * mu * mu + loglik_term(mu, ybit != 0);
+                        if (t < -5.0) wrong_side += 1.0;
                     }
                 }
             }
