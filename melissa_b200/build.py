@@ -33,6 +33,7 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
     cmd = [nvcc_path(), "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
            "-Xcompiler", "-fPIC", "-shared", "-I", os.path.join(ROOT, "include"),
            "-I", os.path.join(PKG_DIR, "csrc"), "-o", LIB_PATH] + SOURCES
+    cmd += os.environ.get("MELISSA_NVCC_FLAGS", "").split()      # e.g. -DSWEEP_XU=2 for tuning experiments
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
     res = subprocess.run(cmd, capture_output=True, text=True)

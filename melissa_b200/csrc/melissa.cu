@@ -696,54 +696,69 @@ int dev_alloc(Tp **p, int64_t n) {
 // v2 (sliced) host side: layout construction and launchers
 // ---------------------------------------------------------------------------
 struct SliceBuild {   // slices of a contiguous range of cell blocks, built by one host thread
-    std::vector<int32_t> slice_region, slice_len, slice_cb, lane_cell, lane_pair;
-    std::vector<int16_t> lane_len;
+    std::vector<int32_t> slice_region, slice_len, slice_cb, lane_cell, lane_pair, lane_meta;
     std::vector<int64_t> lane_src;
 };
 
-void build_slices_range(int cb_lo, int cb_hi, int Tn, int N, int M, const int64_t *cell_ptr,
+// blk_cells[cb * Tn + j] = global cell at position j of block cb (-1 = none).
+void build_slices_range(int cb_lo, int cb_hi, int Tn, int M, const int32_t *blk_cells, const int64_t *cell_ptr,
                         const int64_t *pair_ptr, const int32_t *pair_region, SliceBuild &out) {
-    std::vector<int32_t> cnt((size_t)M + 1), order;
-    std::vector<int64_t> tmp;
+    std::vector<int32_t> cnt((size_t)M + 1), local_of;
+    std::vector<int64_t> members, sorted;
     for (int cb = cb_lo; cb < cb_hi; ++cb) {
-        const int c0 = cb * Tn, c1 = std::min(N, c0 + Tn);
-        const int64_t p0 = cell_ptr[c0], p1 = cell_ptr[c1];
+        // pairs of the block's cells, bucketed by region (counting sort), remembering the cell's position
         std::fill(cnt.begin(), cnt.end(), 0);
-        for (int64_t p = p0; p < p1; ++p) cnt[(size_t)pair_region[p] + 1]++;
+        int64_t total = 0;
+        for (int j = 0; j < Tn; ++j) {
+            const int c = blk_cells[(size_t)cb * Tn + j];
+            if (c < 0) continue;
+            for (int64_t p = cell_ptr[c]; p < cell_ptr[c + 1]; ++p) cnt[(size_t)pair_region[p] + 1]++;
+            total += cell_ptr[c + 1] - cell_ptr[c];
+        }
         for (int m = 0; m < M; ++m) cnt[(size_t)m + 1] += cnt[m];
-        order.resize((size_t)(p1 - p0));
+        members.resize((size_t)total);
+        local_of.resize((size_t)total);
         {
             std::vector<int32_t> cur(cnt.begin(), cnt.end() - 1);
-            for (int64_t p = p0; p < p1; ++p) order[(size_t)cur[pair_region[p]]++] = (int32_t)(p - p0);
+            for (int j = 0; j < Tn; ++j) {
+                const int c = blk_cells[(size_t)cb * Tn + j];
+                if (c < 0) continue;
+                for (int64_t p = cell_ptr[c]; p < cell_ptr[c + 1]; ++p) {
+                    const int32_t q = cur[pair_region[p]]++;
+                    members[(size_t)q] = p;
+                    local_of[(size_t)q] = j;
+                }
+            }
         }
-        // cell of a pair: pairs are cell-major, recover by walking cell_ptr
-        std::vector<int32_t> cell_of((size_t)(p1 - p0));
-        for (int c = c0; c < c1; ++c)
-            for (int64_t p = cell_ptr[c]; p < cell_ptr[c + 1]; ++p) cell_of[(size_t)(p - p0)] = c;
+        std::vector<int32_t> idx;
         for (int m = 0; m < M; ++m) {
             const int b = cnt[m], e = cnt[(size_t)m + 1];
             if (b == e) continue;
-            // longest first; ties keep cell order
-            std::stable_sort(order.begin() + b, order.begin() + e, [&](int32_t u, int32_t v) {
-                return (pair_ptr[p0 + u + 1] - pair_ptr[p0 + u]) > (pair_ptr[p0 + v + 1] - pair_ptr[p0 + v]);
+            idx.resize((size_t)(e - b));
+            for (int q = 0; q < e - b; ++q) idx[(size_t)q] = b + q;
+            // longest first; ties keep block order
+            std::stable_sort(idx.begin(), idx.end(), [&](int32_t u, int32_t v) {
+                const int64_t pu = members[(size_t)u], pv = members[(size_t)v];
+                return (pair_ptr[pu + 1] - pair_ptr[pu]) > (pair_ptr[pv + 1] - pair_ptr[pv]);
             });
-            for (int q = b; q < e; q += 32) {
-                const int fill = std::min(32, e - q);
-                const int64_t pl = p0 + order[q];
+            for (int q = 0; q < e - b; q += 32) {
+                const int fill = std::min(32, e - b - q);
+                const int64_t pl = members[(size_t)idx[(size_t)q]];
                 out.slice_region.push_back(m);
                 out.slice_cb.push_back(cb);
                 out.slice_len.push_back((int32_t)(pair_ptr[pl + 1] - pair_ptr[pl]));
                 for (int l = 0; l < 32; ++l) {
                     if (l < fill) {
-                        const int64_t p = p0 + order[q + l];
-                        out.lane_cell.push_back(cell_of[(size_t)(p - p0)]);
+                        const int32_t k = idx[(size_t)(q + l)];
+                        const int64_t p = members[(size_t)k];
+                        out.lane_cell.push_back(blk_cells[(size_t)cb * Tn + local_of[(size_t)k]]);
                         out.lane_pair.push_back((int32_t)p);
-                        out.lane_len.push_back((int16_t)(pair_ptr[p + 1] - pair_ptr[p]));
+                        out.lane_meta.push_back((int32_t)(pair_ptr[p + 1] - pair_ptr[p]) | (local_of[(size_t)k] << 16));
                         out.lane_src.push_back(pair_ptr[p]);
                     } else {
                         out.lane_cell.push_back(-1);
                         out.lane_pair.push_back(-1);
-                        out.lane_len.push_back(0);
+                        out.lane_meta.push_back(0);
                         out.lane_src.push_back(0);
                     }
                 }
@@ -766,10 +781,10 @@ void free_sliced(melissa_handle *h) {
     Sliced *sl = h->sl;
     if (!sl) return;
     cudaFree(sl->x_sell); cudaFree(sl->ybits); cudaFree(sl->slice_xbase); cudaFree(sl->slice_ybase);
-    cudaFree(sl->slice_len); cudaFree(sl->slice_region); cudaFree(sl->lane_cell); cudaFree(sl->lane_len);
-    cudaFree(sl->item_begin); cudaFree(sl->item_cb); cudaFree(sl->cb_item_ptr); cudaFree(sl->reg_slice_ptr);
+    cudaFree(sl->slice_len); cudaFree(sl->slice_region); cudaFree(sl->slice_cb); cudaFree(sl->lane_cell);
+    cudaFree(sl->lane_meta); cudaFree(sl->blk_cells); cudaFree(sl->reg_slice_ptr);
     cudaFree(sl->reg_slice); cudaFree(sl->stats); cudaFree(sl->mills_tab); cudaFree(sl->rbf_tab);
-    cudaFree(sl->part); cudaFree(sl->lb_part);
+    cudaFree(sl->slice_counter);
     delete sl;
     h->sl = nullptr;
 }
@@ -793,11 +808,23 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
     const int Tn = sl->Tn;
     sl->NB = (N + Tn - 1) / Tn;
     for (int64_t p = 0; p < P; ++p)
-        if (pair_ptr[p + 1] - pair_ptr[p] > 32767)
-            return fail(MELISSA_ERR_ARG, "pair %lld has more than 32767 CpGs", (long long)p);
+        if (pair_ptr[p + 1] - pair_ptr[p] > 65535)
+            return fail(MELISSA_ERR_ARG, "pair %lld has more than 65535 CpGs", (long long)p);
     std::vector<int64_t> cell_ptr((size_t)N + 1, 0);
     for (int64_t p = 0; p < P; ++p) cell_ptr[(size_t)pair_cell[p] + 1]++;
     for (int n = 0; n < N; ++n) cell_ptr[(size_t)n + 1] += cell_ptr[n];
+    // ---- blocks hold cells of similar coverage (sorted by CpG count), so that the pairs a slice groups
+    //      have similar lengths and little of the lock-step loop is padding
+    std::vector<int32_t> blk_cells((size_t)sl->NB * Tn, -1);
+    {
+        std::vector<int32_t> order((size_t)N);
+        for (int n = 0; n < N; ++n) order[(size_t)n] = n;
+        std::stable_sort(order.begin(), order.end(), [&](int32_t u, int32_t v) {
+            return (pair_ptr[cell_ptr[(size_t)u + 1]] - pair_ptr[cell_ptr[u]]) >
+                   (pair_ptr[cell_ptr[(size_t)v + 1]] - pair_ptr[cell_ptr[v]]);
+        });
+        for (int n = 0; n < N; ++n) blk_cells[(size_t)n] = order[(size_t)n];
+    }
     // ---- slices, built by a few host threads over ranges of cell blocks
     int nthr = (int)std::min<int64_t>(std::max(1u, std::thread::hardware_concurrency()), 16);
     nthr = std::max(1, std::min(nthr, sl->NB));
@@ -808,7 +835,8 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
         for (int t = 0; t < nthr; ++t) {
             const int lo = (int)((int64_t)sl->NB * t / nthr), hi = (int)((int64_t)sl->NB * (t + 1) / nthr);
             th.emplace_back([&, t, lo, hi]() {
-                build_slices_range(lo, hi, Tn, N, M, cell_ptr.data(), pair_ptr, pair_region, parts[(size_t)t]);
+                build_slices_range(lo, hi, Tn, M, blk_cells.data(), cell_ptr.data(), pair_ptr, pair_region,
+                                   parts[(size_t)t]);
             });
         }
         for (auto &t : th) t.join();
@@ -820,7 +848,7 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
         all.slice_cb.insert(all.slice_cb.end(), pt.slice_cb.begin(), pt.slice_cb.end());
         all.lane_cell.insert(all.lane_cell.end(), pt.lane_cell.begin(), pt.lane_cell.end());
         all.lane_pair.insert(all.lane_pair.end(), pt.lane_pair.begin(), pt.lane_pair.end());
-        all.lane_len.insert(all.lane_len.end(), pt.lane_len.begin(), pt.lane_len.end());
+        all.lane_meta.insert(all.lane_meta.end(), pt.lane_meta.begin(), pt.lane_meta.end());
         all.lane_src.insert(all.lane_src.end(), pt.lane_src.begin(), pt.lane_src.end());
         pt = SliceBuild();
     }
@@ -837,28 +865,6 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
     }
     sl->x_len = xo;
     sl->y_len = yo;
-    // ---- work items: runs of slices inside one cell block
-    // a CTA (up to 8 warps) should see >= 16 slices per warp so its prologue (tables, accumulators) amortises
-    const int64_t target_items = std::max<int64_t>(1, (int64_t)h->sm_count * 16);
-    const int64_t per_item = std::max<int64_t>(128, (S + target_items - 1) / target_items);
-    std::vector<int64_t> item_begin;
-    std::vector<int32_t> item_cb, cb_item_ptr((size_t)sl->NB + 1, 0);
-    {
-        int64_t q = 0;
-        for (int cb = 0; cb < sl->NB; ++cb) {
-            cb_item_ptr[(size_t)cb] = (int32_t)item_cb.size();
-            int64_t e = q;
-            while (e < S && all.slice_cb[(size_t)e] == cb) ++e;
-            for (int64_t b = q; b < e; b += per_item) {
-                item_begin.push_back(b);
-                item_cb.push_back(cb);
-            }
-            q = e;
-        }
-        cb_item_ptr[(size_t)sl->NB] = (int32_t)item_cb.size();
-        item_begin.push_back(S);
-    }
-    sl->n_items = (int64_t)item_cb.size();
     // ---- region-major list of slices
     std::vector<int64_t> reg_slice_ptr((size_t)M + 1, 0);
     std::vector<int32_t> reg_slice((size_t)S);
@@ -900,23 +906,24 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
     int64_t *d_src = nullptr;
     if ((rc = upload(&sl->slice_xbase, xbase)) || (rc = upload(&sl->slice_ybase, ybase)) ||
         (rc = upload(&sl->slice_len, all.slice_len)) || (rc = upload(&sl->slice_region, all.slice_region)) ||
-        (rc = upload(&sl->lane_cell, all.lane_cell)) || (rc = upload(&sl->lane_len, all.lane_len)) ||
-        (rc = upload(&sl->item_begin, item_begin)) || (rc = upload(&sl->item_cb, item_cb)) ||
-        (rc = upload(&sl->cb_item_ptr, cb_item_ptr)) || (rc = upload(&sl->reg_slice_ptr, reg_slice_ptr)) ||
+        (rc = upload(&sl->slice_cb, all.slice_cb)) || (rc = upload(&sl->blk_cells, blk_cells)) ||
+        (rc = upload(&sl->lane_cell, all.lane_cell)) || (rc = upload(&sl->lane_meta, all.lane_meta)) ||
+        (rc = upload(&sl->reg_slice_ptr, reg_slice_ptr)) ||
         (rc = upload(&sl->reg_slice, reg_slice)) || (rc = upload(&sl->rbf_tab, rbf_tab)) ||
         (rc = upload(&d_src, all.lane_src)))
         return rc;
     if ((rc = dev_alloc(&sl->x_sell, sl->x_len)) || (rc = dev_alloc(&sl->ybits, sl->y_len)) ||
-        (rc = dev_alloc(&sl->stats, S * h->R * 32)) || (rc = dev_alloc(&sl->mills_tab, MILLS_N))) {
+        (rc = dev_alloc(&sl->stats, S * h->R * 32)) || (rc = dev_alloc(&sl->mills_tab, MILLS_N)) ||
+        (rc = dev_alloc(&sl->slice_counter, 1))) {
         cudaFree(d_src);
         return rc;
     }
     const int grid = (int)((S * 32 + 255) / 256);
-    sell_fill_kernel<<<grid, 256>>>(h->x, h->y, d_src, sl->lane_len, sl->slice_xbase, sl->slice_ybase, sl->slice_len,
+    sell_fill_kernel<<<grid, 256>>>(h->x, h->y, d_src, sl->lane_meta, sl->slice_xbase, sl->slice_ybase, sl->slice_len,
                                     sl->x_sell, sl->ybits, S);
     {
         auto run = [&]() -> int {
-            DISPATCH_D(h->D, hh_sliced_kernel<DD><<<grid, 256>>>(sl->x_sell, sl->slice_xbase, sl->lane_len, sl->stats,
+            DISPATCH_D(h->D, hh_sliced_kernel<DD><<<grid, 256>>>(sl->x_sell, sl->slice_xbase, sl->lane_meta, sl->stats,
                                                                 S, h->basis));
             return MELISSA_OK;
         };
@@ -935,7 +942,7 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
 size_t sweep_v2_smem(const melissa_handle *h, int nw) {
     const Sliced *sl = h->sl;
     return (size_t)sl->rt.n_entries * sizeof(double2) +
-           ((size_t)MILLS_N + 1 + (size_t)sl->Tn * h->K * (1 + nw) + (size_t)nw * h->K * h->R) * sizeof(double);
+           ((size_t)MILLS_N + 1 + (size_t)sl->Tn * h->K * nw + (size_t)nw * h->K * h->R) * sizeof(double);
 }
 
 int sweep_v2_warps(const melissa_handle *h) {
@@ -953,17 +960,25 @@ int launch_sweep_v2(melissa_handle *h, bool with_lb, bool uniform_r) {
     const size_t smem = sweep_v2_smem(h, nw);
     SweepV2Args a;
     a.x_sell = sl->x_sell; a.ybits = sl->ybits; a.slice_xbase = sl->slice_xbase; a.slice_ybase = sl->slice_ybase;
-    a.slice_len = sl->slice_len; a.slice_region = sl->slice_region; a.lane_cell = sl->lane_cell; a.lane_len = sl->lane_len;
-    a.item_begin = sl->item_begin; a.item_cb = sl->item_cb; a.stats = sl->stats; a.U = h->U; a.r = h->r;
-    a.part = sl->part; a.lb_part = sl->lb_part; a.mills_tab = sl->mills_tab; a.rbf_tab = sl->rbf_tab; a.rt = sl->rt;
+    a.slice_len = sl->slice_len; a.slice_region = sl->slice_region; a.slice_cb = sl->slice_cb;
+    a.lane_cell = sl->lane_cell; a.lane_meta = sl->lane_meta; a.blk_cells = sl->blk_cells;
+    a.stats = sl->stats; a.U = h->U; a.r = h->r; a.log_rho = h->log_rho; a.lbbuf = h->lbbuf;
+    a.mills_tab = sl->mills_tab; a.rbf_tab = sl->rbf_tab; a.rt = sl->rt;
     a.basis = h->basis; a.K = h->K; a.Tn = sl->Tn; a.N = h->N;
-    const int grid = (int)sl->n_items, block = 32 * nw;
+    a.slice_counter = sl->slice_counter; a.S = sl->S;
+    const int block = 32 * nw;
+    int grid = 1;
+    CU(cudaMemsetAsync(sl->slice_counter, 0, sizeof(unsigned long long), h->stream));
+    if (with_lb) CU(cudaMemsetAsync(h->lbbuf, 0, 2 * sizeof(double), h->stream));
     prof_begin(h, MELISSA_KERNEL_SWEEP);
 #define SWEEP2(LB_, UNI_)                                                                                   \
     DISPATCH_D(h->D, {                                                                                      \
         auto kfn = sweep_v2_kernel<DD, LB_, UNI_>;                                                          \
         CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));              \
         CU(cudaFuncSetAttribute(kfn, cudaFuncAttributePreferredSharedMemoryCarveout, 100));                 \
+        int per_sm = 1;                                                                                     \
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, block, smem));                       \
+        grid = (int)std::min<int64_t>((sl->S + nw - 1) / nw, (int64_t)h->sm_count * std::max(1, per_sm));  \
         kfn<<<grid, block, smem, h->stream>>>(a);                                                           \
     })
     if (with_lb && uniform_r) { SWEEP2(true, true) }
@@ -973,11 +988,6 @@ int launch_sweep_v2(melissa_handle *h, bool with_lb, bool uniform_r) {
 #undef SWEEP2
     prof_end(h);
     CU(cudaGetLastError());
-    if (with_lb) {
-        lb_reduce_kernel<<<1, 256, 0, h->stream>>>(sl->lb_part, sl->n_items, h->lbbuf);
-        h->launches++;
-        CU(cudaGetLastError());
-    }
     return MELISSA_OK;
 }
 
@@ -998,10 +1008,6 @@ void free_fit(melissa_handle *h) {
     cudaFree(h->U); cudaFree(h->Spk); cudaFree(h->r); cudaFree(h->log_r); cudaFree(h->log_rho);
     cudaFree(h->red); cudaFree(h->lbbuf); cudaFree(h->scal_mem);
     h->U = h->Spk = h->r = h->log_r = h->log_rho = h->red = h->lbbuf = h->scal_mem = nullptr;
-    if (h->sl) {
-        cudaFree(h->sl->part); cudaFree(h->sl->lb_part);
-        h->sl->part = h->sl->lb_part = nullptr;
-    }
     h->begun = false;
 }
 
@@ -1302,8 +1308,6 @@ int melissa_vb_begin(melissa_handle *h, int32_t K, const double *w0, const doubl
     CU(cudaGetLastError());
     h->begun = true;
     if (h->sl) {
-        if ((rc = dev_alloc(&h->sl->part, h->sl->n_items * h->sl->Tn * K))) return rc;
-        if ((rc = dev_alloc(&h->sl->lb_part, h->sl->n_items * 2))) return rc;
         if (sweep_v2_warps(h) == 0)
             return fail(MELISSA_ERR_ARG, "K = %d does not fit the sweep's shared memory at cell block %d", K, h->sl->Tn);
     }
@@ -1318,12 +1322,7 @@ int melissa_vb_phase_a(melissa_handle *h) {
     CU(cudaMemsetAsync(h->red, 0, (size_t)h->red_len * sizeof(double), h->stream));
     double *colsum = h->red + MK * h->R, *rlogr = colsum + h->K;
     prof_begin(h, MELISSA_KERNEL_RESP);
-    if (h->sl)
-        resp_v2_kernel<<<(h->N + 127) / 128, 128, 0, h->stream>>>(h->sl->part, h->sl->cb_item_ptr, h->sc.elogpi, h->r,
-                                                                 h->log_r, colsum, rlogr, h->sc.Eww_acc,
-                                                                 h->sc.logdet_acc, h->N, h->K, h->sl->Tn);
-    else
-        resp_kernel<<<(h->N + 127) / 128, 128, 0, h->stream>>>(h->log_rho, h->sc.elogpi, h->r, h->log_r, colsum,
+    resp_kernel<<<(h->N + 127) / 128, 128, 0, h->stream>>>(h->log_rho, h->sc.elogpi, h->r, h->log_r, colsum,
                                                               rlogr, h->sc.Eww_acc, h->sc.logdet_acc, h->N, h->K);
     prof_end(h);
     CU(cudaGetLastError());

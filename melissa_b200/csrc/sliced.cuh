@@ -21,7 +21,10 @@ constexpr int MILLS_SP = 128;                 // table points per unit of t
 constexpr int MILLS_HALF = 8 * MILLS_SP;      // t in [-8, 8]
 constexpr int MILLS_N = 2 * MILLS_HALF + 1;
 #ifndef SWEEP_XU
-#define SWEEP_XU 4
+#define SWEEP_XU 2
+#endif
+#ifndef SWEEP_MINB
+#define SWEEP_MINB 3
 #endif
 constexpr int RBF_SUB = 128;                  // table points per centre spacing
 constexpr double MAGIC = 6755399441055744.0;  // 1.5 * 2^52: (v + MAGIC) - MAGIC rounds v to an integer
@@ -29,24 +32,22 @@ constexpr double MAGIC = 6755399441055744.0;  // 1.5 * 2^52: (v + MAGIC) - MAGIC
 struct Sliced {
     bool on = false;
     int Tn = 128, NB = 0;
-    int64_t S = 0, n_items = 0, x_len = 0, y_len = 0;
+    int64_t S = 0, x_len = 0, y_len = 0;
     double *x_sell = nullptr;
     uint32_t *ybits = nullptr;
     int64_t *slice_xbase = nullptr, *slice_ybase = nullptr;
     int32_t *slice_len = nullptr, *slice_region = nullptr;
-    int32_t *lane_cell = nullptr;
-    int16_t *lane_len = nullptr;
-    int64_t *item_begin = nullptr;        // [n_items + 1] slice ranges
-    int32_t *item_cb = nullptr;           // [n_items]
-    int32_t *cb_item_ptr = nullptr;       // [NB + 1]
+    int32_t *slice_cb = nullptr;          // [S] cell block of the slice
+    int32_t *lane_cell = nullptr;         // [S*32] global cell index, -1 = padding lane
+    int32_t *lane_meta = nullptr;         // [S*32] CpG count | (position of the cell in its block << 16)
+    int32_t *blk_cells = nullptr;         // [NB*Tn] global cell index of each block position, -1 = none
     int64_t *reg_slice_ptr = nullptr;     // [M + 1]
     int32_t *reg_slice = nullptr;         // [S]
     double *stats = nullptr;              // [S][R][32]
     double *mills_tab = nullptr;          // [MILLS_N]
     double2 *rbf_tab = nullptr;           // [rt.n_entries] (E(u0), B(u0))
     RbfTab rt{};
-    double *part = nullptr;               // [n_items][Tn][K]   (per fit)
-    double *lb_part = nullptr;            // [n_items][2]       (per fit)
+    unsigned long long *slice_counter = nullptr;   // slice dispenser of the persistent sweep
     std::vector<int32_t> lane_pair;       // host: original pair of (slice, lane), -1 = padding
 };
 
@@ -201,7 +202,7 @@ __device__ __forceinline__ double trunc_mean_fast(double t, const double *__rest
 
 // Re-lay x / y into slices.  One thread per (slice, lane).
 __global__ void sell_fill_kernel(const double *__restrict__ x, const uint8_t *__restrict__ y,
-                                 const int64_t *__restrict__ lane_src, const int16_t *__restrict__ lane_len,
+                                 const int64_t *__restrict__ lane_src, const int32_t *__restrict__ lane_meta,
                                  const int64_t *__restrict__ slice_xbase, const int64_t *__restrict__ slice_ybase,
                                  const int32_t *__restrict__ slice_len, double *__restrict__ x_sell,
                                  uint32_t *__restrict__ ybits, int64_t S) {
@@ -209,7 +210,7 @@ __global__ void sell_fill_kernel(const double *__restrict__ x, const uint8_t *__
     if (t >= S * 32) return;
     const int64_t s = t >> 5;
     const int lane = (int)(t & 31);
-    const int L = slice_len[s], len = lane_len[t];
+    const int L = slice_len[s], len = lane_meta[t] & 0xffff;
     const int64_t src = lane_src[t], xb = slice_xbase[s], yb = slice_ybase[s];
     uint32_t word = 0;
     for (int i = 0; i < L; ++i) {
@@ -229,14 +230,14 @@ __global__ void sell_fill_kernel(const double *__restrict__ x, const uint8_t *__
 // H^T H per pair into stats[slice][D + t][lane]; g rows zeroed.  One thread per (slice, lane).
 template <int D>
 __global__ void hh_sliced_kernel(const double *__restrict__ x_sell, const int64_t *__restrict__ slice_xbase,
-                                 const int16_t *__restrict__ lane_len, double *__restrict__ stats, int64_t S,
+                                 const int32_t *__restrict__ lane_meta, double *__restrict__ stats, int64_t S,
                                  BasisDev basis) {
     constexpr int T = D * (D + 1) / 2, R = D + T;
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= S * 32) return;
     const int64_t s = t >> 5;
     const int lane = (int)(t & 31);
-    const int len = lane_len[t];
+    const int len = lane_meta[t] & 0xffff;
     const int64_t xb = slice_xbase[s];
     double hh[T];
 #pragma unroll
@@ -261,67 +262,78 @@ struct SweepV2Args {
     const double *x_sell;
     const uint32_t *ybits;
     const int64_t *slice_xbase, *slice_ybase;
-    const int32_t *slice_len, *slice_region, *lane_cell;
-    const int16_t *lane_len;
-    const int64_t *item_begin;
-    const int32_t *item_cb;
+    const int32_t *slice_len, *slice_region, *slice_cb, *lane_cell, *lane_meta, *blk_cells;
     double *stats;
     const double *U, *r;
-    double *part, *lb_part;
+    double *log_rho, *lbbuf;
     const double *mills_tab;
     const double2 *rbf_tab;
     RbfTab rt;
     BasisDev basis;
     int K, Tn, N;
+    unsigned long long *slice_counter;
+    int64_t S;
 };
 
 // The per-CpG sweep on slices (R/melissa_vb.R:418-435 refresh + the next iteration's
-// E-step terms :322-327 + lb_pz_qz :469-473 when WITH_LB).  One CTA per work item (a
-// run of slices of one cell block), one warp per slice.
+// E-step terms :322-327 + lb_pz_qz :469-473 when WITH_LB).
+// Persistent CTAs load the two function tables once; after that every WARP is on its
+// own: it claims slices one at a time from a global counter (slices are short, ~7 us,
+// so there is no tail and no CTA barrier), keeps the E-step sums of its current cell
+// block in a private shared-memory array indexed by the cell's position in the block,
+// and adds that array to log_rho when it moves on to another block.
 template <int D, bool WITH_LB, bool UNIFORM_R>
-__global__ void __launch_bounds__(256, 2) sweep_v2_kernel(SweepV2Args a) {
+__global__ void __launch_bounds__(256, SWEEP_MINB) sweep_v2_kernel(SweepV2Args a) {
     constexpr int T = D * (D + 1) / 2, R = D + T;
     constexpr int XU = SWEEP_XU;                // CpG rows fetched per group (prefetch distance, ILP)
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    __shared__ unsigned long long s_next;       // next unclaimed slice of this work item
     const int K = a.K, Tn = a.Tn;
     const int nw = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    // shared: rbf table | mills table | r block | per-warp U staging | per-warp accumulators
+    // shared: rbf table | mills table | per-warp U staging | per-warp accumulators
     double2 *s_rbf = reinterpret_cast<double2 *>(smem_raw);
     double *s_mills = reinterpret_cast<double *>(s_rbf + a.rt.n_entries);
-    double *s_r = s_mills + MILLS_N + 1;
-    double *s_u = s_r + Tn * K;
+    double *s_u = s_mills + MILLS_N + 1;
     double *s_acc = s_u + nw * K * R;
-    const int item = blockIdx.x;
-    const int cb = a.item_cb[item];
-    const int cell0 = cb * Tn;
-    const int64_t s_begin = a.item_begin[item], s_end = a.item_begin[item + 1];
-    if (threadIdx.x == 0) s_next = (unsigned long long)s_begin;
     for (int i = threadIdx.x; i < a.rt.n_entries; i += blockDim.x) s_rbf[i] = a.rbf_tab[i];
     for (int i = threadIdx.x; i < MILLS_N; i += blockDim.x) s_mills[i] = a.mills_tab[i];
-    const double inv_K = 1.0 / (double)K;
-    for (int i = threadIdx.x; i < Tn * K; i += blockDim.x) {
-        const int n = cell0 + i / K;
-        s_r[i] = UNIFORM_R ? inv_K : (n < a.N ? a.r[(int64_t)cell0 * K + i] : 0.0);
-    }
     for (int i = threadIdx.x; i < nw * Tn * K; i += blockDim.x) s_acc[i] = 0.0;
     __syncthreads();
+    const double inv_K = 1.0 / (double)K;
     double *my_u = s_u + warp * K * R;
     double *my_acc = s_acc + warp * Tn * K;
     double lb_local = 0.0, wrong_side = 0.0;
-    for (;;) {
-        // slices differ in length (longest pairs first inside a region), so warps take them on demand
-        unsigned long long claimed = 0;
-        if (lane == 0) claimed = atomicAdd(&s_next, 1ull);
-        const int64_t s = (int64_t)__shfl_sync(0xffffffffu, claimed, 0);
-        if (s >= s_end) break;
+    int cur_cb = -1;
+    auto claim = [&]() -> int64_t {
+        unsigned long long c = 0;
+        if (lane == 0) c = atomicAdd(a.slice_counter, 1ull);
+        return (int64_t)__shfl_sync(0xffffffffu, c, 0);
+    };
+    auto flush = [&]() {                        // private sums of block cur_cb -> log_rho, then clear
+        if (cur_cb < 0) return;
+        __syncwarp();
+        for (int i = lane; i < Tn * K; i += 32) {
+            const double v = my_acc[i];
+            const int cell = a.blk_cells[(int64_t)cur_cb * Tn + i / K];
+            if (cell >= 0 && v != 0.0) atomicAdd(&a.log_rho[(int64_t)cell * K + i % K], v);
+            my_acc[i] = 0.0;
+        }
+        __syncwarp();
+    };
+    int64_t s = claim();
+    while (s < a.S) {
+        const int64_t s_following = claim();    // claimed early: its round trip hides behind this slice
+        const int cb = a.slice_cb[s];
+        if (cb != cur_cb) {
+            flush();
+            cur_cb = cb;
+        }
         const int m = a.slice_region[s];
         const int L = a.slice_len[s];
         const int64_t xb = a.slice_xbase[s], yb = a.slice_ybase[s];
         const int cell = a.lane_cell[s * 32 + lane];
-        const int len = a.lane_len[s * 32 + lane];
+        const int meta = a.lane_meta[s * 32 + lane];
+        const int len = meta & 0xffff, nl = meta >> 16;
         const bool valid = cell >= 0;
-        const int nl = valid ? cell - cell0 : 0;
         const double *xrow = a.x_sell + xb + lane;
         double xa[XU];
 #pragma unroll
@@ -340,7 +352,7 @@ __global__ void __launch_bounds__(256, 2) sweep_v2_kernel(SweepV2Args a) {
         for (int d = 0; d < D; ++d) wbar[d] = 0.0;
         for (int k = 0; k < K; ++k) {
             const double *u = my_u + k * R;
-            const double rk = s_r[nl * K + k];
+            const double rk = UNIFORM_R ? inv_K : (valid ? a.r[(int64_t)cell * K + k] : 0.0);
             double trc = 0.0;
 #pragma unroll
             for (int q = 0; q < T; ++q) trc = fma(u[D + q], hh[q], trc);
@@ -412,81 +424,17 @@ __global__ void __launch_bounds__(256, 2) sweep_v2_kernel(SweepV2Args a) {
                 my_acc[nl * K + k] += lin;
             }
         }
+        s = s_following;
     }
-    __syncthreads();
-    double *out = a.part + (int64_t)item * Tn * K;
-    for (int i = threadIdx.x; i < Tn * K; i += blockDim.x) {
-        double v = 0.0;
-        for (int w = 0; w < nw; ++w) v += s_acc[w * Tn * K + i];
-        out[i] = v;
-    }
+    flush();
     if (WITH_LB) {
-        __shared__ double red_smem[32];
-        double v = block_sum(lb_local, red_smem);
-        if (threadIdx.x == 0) a.lb_part[2 * item] = v;
-        v = block_sum(wrong_side, red_smem);
-        if (threadIdx.x == 0) a.lb_part[2 * item + 1] = v;
-    }
-}
-
-// Sum the per-item lower-bound partials in a fixed order.
-__global__ void lb_reduce_kernel(const double *__restrict__ lb_part, int64_t n_items, double *__restrict__ lbbuf) {
-    __shared__ double red_smem[32];
-    double a = 0.0, b = 0.0;
-    for (int64_t i = threadIdx.x; i < n_items; i += blockDim.x) {
-        a += lb_part[2 * i];
-        b += lb_part[2 * i + 1];
-    }
-    a = block_sum(a, red_smem);
-    b = block_sum(b, red_smem);
-    if (threadIdx.x == 0) {
-        lbbuf[0] = a;
-        lbbuf[1] = b;
-    }
-}
-
-// Responsibilities from the per-item E-step partials (v2 twin of resp_kernel).
-__global__ void __launch_bounds__(128)
-resp_v2_kernel(const double *__restrict__ part, const int32_t *__restrict__ cb_item_ptr,
-               const double *__restrict__ elogpi, double *__restrict__ r, double *__restrict__ log_r,
-               double *__restrict__ colsum, double *__restrict__ rlogr, double *__restrict__ Eww_acc,
-               double *__restrict__ logdet_acc, int N, int K, int Tn) {
-    __shared__ double red_smem[32];
-    const int n = blockIdx.x * blockDim.x + threadIdx.x;
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        *logdet_acc = 0.0;
-        for (int k = 0; k < K; ++k) Eww_acc[k] = 0.0;
-    }
-    double lse = 0.0, rl = 0.0;
-    const int cb = n < N ? n / Tn : 0, nl = n < N ? n % Tn : 0;
-    const int i0 = n < N ? cb_item_ptr[cb] : 0, i1 = n < N ? cb_item_ptr[cb + 1] : 0;
-    if (n < N) {
-        double mx = -INFINITY;
-        for (int k = 0; k < K; ++k) {
-            double v = 0.0;
-            for (int it = i0; it < i1; ++it) v += part[((int64_t)it * Tn + nl) * K + k];
-            v += elogpi[k];
-            log_r[(int64_t)n * K + k] = v;                      // log rho for now
-            mx = fmax(mx, v);
+        lb_local = warp_sum(lb_local);
+        wrong_side = warp_sum(wrong_side);
+        if (lane == 0) {
+            atomicAdd(&a.lbbuf[0], lb_local);
+            if (wrong_side != 0.0) atomicAdd(&a.lbbuf[1], wrong_side);
         }
-        double s = 0.0;
-        for (int k = 0; k < K; ++k) s += exp(log_r[(int64_t)n * K + k] - mx);
-        lse = log(s) + mx;                                      // R/utils.R:16-20
     }
-    for (int k = 0; k < K; ++k) {
-        double rk = 0.0;
-        if (n < N) {
-            const double lr = log_r[(int64_t)n * K + k] - lse;
-            rk = exp(lr);
-            log_r[(int64_t)n * K + k] = lr;
-            r[(int64_t)n * K + k] = rk;
-            rl += rk * lr;
-        }
-        const double s = block_sum(rk, red_smem);
-        if (threadIdx.x == 0) atomicAdd(&colsum[k], s);
-    }
-    const double s = block_sum(rl, red_smem);
-    if (threadIdx.x == 0) atomicAdd(rlogr, s);
 }
 
 // Contraction on slices: acc[m,k,j] = sum over the region's slices and lanes of

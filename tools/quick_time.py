@@ -14,6 +14,9 @@ N, M, K = (int(a) for a in sys.argv[1:4]) if len(sys.argv) > 3 else (1000, 1000,
 t0 = time.time()
 d, tr = synth.generate(N, M, K, n_basis=4, seed=1)
 t_gen = time.time() - t0
+import os
+if os.environ.get('MELISSA_TN'):
+    mb.set_option('cell_block', int(os.environ['MELISSA_TN']))
 t0 = time.time()
 eng = mb.Engine(d, tr["basis"])
 t_pack = time.time() - t0
