@@ -158,7 +158,9 @@ def main():
     group = None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
+        import datetime
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"),
+                                timeout=datetime.timedelta(seconds=180))
         group = dist.group.WORLD
     # ---- this rank's cell shard, generated on the device
     per = -(-wl["N"] // world)
@@ -219,12 +221,12 @@ def main():
         dist.all_reduce(ms, op=dist.ReduceOp.MAX, group=group)
     ms = float(ms[0])
     launches = eng.launch_count() - launches0
-    # keep the GPU busy a little longer so the clock sampler sees the loaded state, then read it
+    # keep the GPU busy ~1 s longer so the clock sampler sees the loaded state; the count is derived from
+    # the rank-agreed time so that every rank issues the same collectives
+    for _ in range(int(min(400, max(1, 1000.0 / max(ms / steps, 1e-3))))):
+        step()
+    torch.cuda.synchronize()
     if sampler:
-        t_end = time.time() + 1.0
-        while time.time() < t_end:
-            step()
-        torch.cuda.synchronize()
         clocks = sampler.finish()
     # ---- per-kernel durations (CUDA events on the launching stream), separate pass
     eng.profile(True)
@@ -263,8 +265,12 @@ def main():
         try:
             import psutil
             need = nnz_loc * 9 + P_loc * 16 + 4096
-            if psutil.virtual_memory().available < 2.5 * need:
-                raise MemoryError("host RAM too small for a pinned copy of the shard")
+            fits = torch.tensor([1.0 if psutil.virtual_memory().available > 2.5 * need * world else 0.0],
+                                dtype=torch.float64, device="cuda")
+            if group is not None:                                  # all ranks take the same branch
+                dist.all_reduce(fits, op=dist.ReduceOp.MIN, group=group)
+            if float(fits[0]) == 0.0:
+                raise MemoryError("host RAM too small for a pinned copy of the shards")
             host = {}
             for k in ("pair_ptr", "pair_cell", "pair_region", "x", "y"):
                 t = torch.empty(data_t[k].shape, dtype=data_t[k].dtype, pin_memory=True)
