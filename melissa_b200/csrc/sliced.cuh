@@ -134,6 +134,23 @@ __device__ __forceinline__ void eval_basis_tab(double x, const RbfTab &rt, const
     }
 }
 
+// Series coefficients that are not exactly representable in a 32-bit immediate live in
+// constant memory: a DFMA can take one operand straight from the constant bank, whereas a
+// literal costs two register moves every time the (register-starved) loop needs it again.
+#ifndef COEF_CONST
+#define COEF_CONST 1
+#endif
+#if COEF_CONST
+__constant__ double kInvFactC[8] = {1.0, 1.0, 0.5, 1.0 / 6, 1.0 / 24, 1.0 / 120, 1.0 / 720, 1.0 / 5040};
+__constant__ double kInvIntC[7] = {0.0, 1.0, 0.5, 1.0 / 3, 0.25, 0.2, 1.0 / 6};
+#define kInvFact(i) kInvFactC[i]
+#define kInvInt(i) kInvIntC[i]
+#else
+__host__ __device__ constexpr double inv_fact_lit(int i) { return i <= 1 ? 1.0 : inv_fact_lit(i - 1) / i; }
+#define kInvFact(i) inv_fact_lit(i)
+#define kInvInt(i) (1.0 / (i))
+#endif
+
 // Branch-free twins of the two table functions for the sweep's inner loop: the table
 // index is clamped instead of tested, and the (never expected) out-of-range case is
 // reported through the return value so the caller can redo that CpG on the slow path.
@@ -152,19 +169,19 @@ __device__ __forceinline__ bool eval_basis_fast(double x, const RbfTab &rt, cons
     const double d = u - u0;
     const double2 eb = tab[idx];
     const double w = (rt.neg_gamma * d) * fma(2.0, u0, d);
-    double c = fma(w, 1.0 / 5040, 1.0 / 720);
-    c = fma(w, c, 1.0 / 120);
-    c = fma(w, c, 1.0 / 24);
-    c = fma(w, c, 1.0 / 6);
+    double c = fma(w, kInvFact(7), kInvFact(6));
+    c = fma(w, c, kInvFact(5));
+    c = fma(w, c, kInvFact(4));
+    c = fma(w, c, kInvFact(3));
     c = fma(w, c, 0.5);
     c = fma(w, c, 1.0);
     c = fma(w, c, 1.0);
     h[1] = eb.x * c;
     if (D > 2) {
         const double z = rt.g2d * d;
-        double e = fma(z, 1.0 / 720, 1.0 / 120);
-        e = fma(z, e, 1.0 / 24);
-        e = fma(z, e, 1.0 / 6);
+        double e = fma(z, kInvFact(6), kInvFact(5));
+        e = fma(z, e, kInvFact(4));
+        e = fma(z, e, kInvFact(3));
         e = fma(z, e, 0.5);
         e = fma(z, e, 1.0);
         e = fma(z, e, 1.0);
@@ -187,10 +204,10 @@ __device__ __forceinline__ double trunc_mean_fast(double t, const double *__rest
     const double R0 = tab[i + MILLS_HALF];
     const double c1 = fma(t0, R0, 1.0);
     const double c2 = 0.5 * fma(t0, c1, R0);
-    const double c3 = (1.0 / 3.0) * fma(t0, c2, c1);
+    const double c3 = fma(t0, c2, c1) * kInvInt(3);
     const double c4 = 0.25 * fma(t0, c3, c2);
-    const double c5 = 0.2 * fma(t0, c4, c3);
-    const double c6 = (1.0 / 6.0) * fma(t0, c5, c4);
+    const double c5 = fma(t0, c4, c3) * kInvInt(5);
+    const double c6 = fma(t0, c5, c4) * kInvInt(6);
     double R = fma(d, c6, c5);
     R = fma(d, R, c4);
     R = fma(d, R, c3);
@@ -256,6 +273,37 @@ __global__ void hh_sliced_kernel(const double *__restrict__ x_sell, const int64_
     for (int d = 0; d < D; ++d) rec[d * 32] = 0.0;
 #pragma unroll
     for (int q = 0; q < T; ++q) rec[(D + q) * 32] = hh[q];
+}
+
+// Rare path of the sweep's inner loop (x outside the table, |s mu| >= 8): plain exp / erfcx
+// evaluation of one CpG.  Kept out of line so it costs the hot loop no registers.
+template <int D>
+struct CpgSlow {
+    double h[D];
+    double mu, t, G;
+};
+template <int D>
+struct WBar {
+    double w[D];
+};
+#ifndef SLOW_INLINE
+#define SLOW_INLINE 1
+#endif
+#if SLOW_INLINE
+#define SLOW_ATTR __forceinline__
+#else
+#define SLOW_ATTR __noinline__
+#endif
+template <int D>
+__device__ SLOW_ATTR CpgSlow<D> cpg_slow(double x, uint32_t ybit, WBar<D> wb, const BasisDev *basis) {
+    CpgSlow<D> o;
+    eval_basis<D>(x, *basis, o.h);
+    o.mu = wb.w[0];
+#pragma unroll
+    for (int d = 1; d < D; ++d) o.mu = fma(o.h[d], wb.w[d], o.mu);
+    o.t = ybit ? o.mu : -o.mu;
+    o.G = trunc_mean(o.t);
+    return o;
 }
 
 struct SweepV2Args {
@@ -389,14 +437,17 @@ __global__ void __launch_bounds__(256, SWEEP_MINB) sweep_v2_kernel(SweepV2Args a
                 bool bad_t;
                 double G = trunc_mean_fast(t, s_mills, bad_t);
                 if (__any_sync(0xffffffffu, (bad || bad_t) && live)) {     // never taken on sane data
-                    if (bad) {
-                        eval_basis<D>(xa[u], a.basis, h);
-                        mu = wbar[0];
+                    if (bad || bad_t) {
+                        WBar<D> wb;
 #pragma unroll
-                        for (int d = 1; d < D; ++d) mu = fma(h[d], wbar[d], mu);
-                        t = ybit ? mu : -mu;
+                        for (int d = 0; d < D; ++d) wb.w[d] = wbar[d];
+                        const CpgSlow<D> o = cpg_slow<D>(xa[u], ybit, wb, &a.basis);
+#pragma unroll
+                        for (int d = 0; d < D; ++d) h[d] = o.h[d];
+                        mu = o.mu;
+                        t = o.t;
+                        G = o.G;
                     }
-                    if (bad || bad_t) G = trunc_mean(t);
                 }
                 const double Ez = __hiloint2double((__double2hiint(G) ^ sflip) & live, __double2loint(G) & live);
                 g[0] += Ez;
