@@ -96,6 +96,7 @@ int melissa_pack_device(int32_t n_cells, int32_t n_regions, int64_t n_pairs,
  *   "sliced"      -1 = use the sliced layout whenever the RBF centres are equally
  *                 spaced (default), 0 = always the flat cell-major layout, 1 = require
  *                 the sliced layout (pack fails if it cannot be used)
+ *   "contract_mma" 1 = FP64 tensor-core contraction (default), 0 = CUDA-core contraction
  */
 int melissa_set_option(const char *key, int64_t value);
 

@@ -991,14 +991,45 @@ int launch_sweep_v2(melissa_handle *h, bool with_lb, bool uniform_r) {
     return MELISSA_OK;
 }
 
+int g_opt_contract_mma = 1;
+
+template <int MT, int NT>
+int launch_contract_mma_t(melissa_handle *h, int block) {
+    Sliced *sl = h->sl;
+    const size_t smem = (size_t)(block / 32) * MT * NT * 64 * sizeof(double);
+    auto kfn = contract_mma_kernel<MT, NT>;
+    if (smem > 48 * 1024) CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kfn<<<h->M, block, smem, h->stream>>>(sl->reg_slice_ptr, sl->reg_slice, sl->lane_cell, sl->stats, h->r, h->red,
+                                         h->K, h->R);
+    return MELISSA_OK;
+}
+
 int launch_contract_v2(melissa_handle *h) {
     Sliced *sl = h->sl;
-    constexpr int JC = 5, KC = 4;
-    const int combos = ((h->R + JC - 1) / JC) * ((h->K + KC - 1) / KC);
-    const int block = 32 * std::min(8, combos);
+    const int MT = (h->K + 7) / 8, NT = (h->R + 7) / 8;
     prof_begin(h, MELISSA_KERNEL_CONTRACT);
-    contract_v2_kernel<JC, KC><<<h->M, block, 0, h->stream>>>(sl->reg_slice_ptr, sl->reg_slice, sl->lane_cell, sl->stats,
-                                                             h->r, h->red, h->K, h->R);
+    bool done = false;
+    if (g_opt_contract_mma && MT <= 4 && NT <= 6) {
+        // warps per region: enough to keep >= ~32 warps per SM in flight, not more than the region has slices
+        const int64_t avg_slices = std::max<int64_t>(1, sl->S / std::max(1, h->M));
+        int nw = 8;
+        while (nw > 1 && avg_slices / nw < 4) nw >>= 1;
+        const int block = 32 * nw;
+        int rc = MELISSA_OK;
+#define CMMA(MT_, NT_) if (MT == MT_ && NT == NT_) { rc = launch_contract_mma_t<MT_, NT_>(h, block); done = true; }
+        CMMA(1, 1) CMMA(1, 2) CMMA(1, 3) CMMA(1, 4) CMMA(1, 5) CMMA(1, 6)
+        CMMA(2, 1) CMMA(2, 2) CMMA(2, 3) CMMA(2, 4) CMMA(2, 5) CMMA(2, 6)
+        CMMA(3, 3) CMMA(3, 6) CMMA(4, 3) CMMA(4, 6)
+#undef CMMA
+        if (rc) return rc;
+    }
+    if (!done) {
+        constexpr int JC = 5, KC = 4;
+        const int combos = ((h->R + JC - 1) / JC) * ((h->K + KC - 1) / KC);
+        const int block = 32 * std::min(8, combos);
+        contract_v2_kernel<JC, KC><<<h->M, block, 0, h->stream>>>(sl->reg_slice_ptr, sl->reg_slice, sl->lane_cell,
+                                                                 sl->stats, h->r, h->red, h->K, h->R);
+    }
     prof_end(h);
     CU(cudaGetLastError());
     return MELISSA_OK;
@@ -1200,6 +1231,10 @@ int melissa_set_option(const char *key, int64_t value) {
     if (!std::strcmp(key, "cell_block")) {
         if (value < 1 || value > 4096) return fail(MELISSA_ERR_ARG, "cell_block must be in 1..4096");
         g_opt_cell_block = (int)value;
+        return MELISSA_OK;
+    }
+    if (!std::strcmp(key, "contract_mma")) {
+        g_opt_contract_mma = value != 0;
         return MELISSA_OK;
     }
     if (!std::strcmp(key, "sliced")) {
@@ -1447,15 +1482,15 @@ int melissa_vb_fetch_HtEz(melissa_handle *h, double *out) {
     CU(cudaStreamSynchronize(h->stream));
     if (h->sl) {
         const Sliced *sl = h->sl;
-        const size_t row = (size_t)h->D * 32;
-        std::vector<double> buf((size_t)sl->S * row);
-        CU(cudaMemcpy2D(buf.data(), row * sizeof(double), sl->stats, (size_t)h->R * 32 * sizeof(double),
-                        row * sizeof(double), (size_t)sl->S, cudaMemcpyDeviceToHost));
+        const size_t rec = (size_t)h->R * 32;
+        std::vector<double> buf((size_t)sl->S * rec);
+        CU(cudaMemcpy(buf.data(), sl->stats, buf.size() * sizeof(double), cudaMemcpyDeviceToHost));
         for (int64_t q = 0; q < sl->S; ++q)
             for (int l = 0; l < 32; ++l) {
                 const int32_t p = sl->lane_pair[(size_t)q * 32 + l];
                 if (p < 0) continue;
-                for (int d = 0; d < h->D; ++d) out[(size_t)p * h->D + d] = buf[(size_t)q * row + (size_t)d * 32 + l];
+                for (int d = 0; d < h->D; ++d)
+                    out[(size_t)p * h->D + d] = buf[(size_t)q * rec + ((size_t)(l >> 2) * h->R + d) * 4 + (l & 3)];
             }
         return MELISSA_OK;
     }

@@ -5,9 +5,12 @@
 // warp's unit of work: lane l owns pair (cell_l, m); CpG i of every lane sits in one
 // 256-byte row x_sell[xbase + 32 i + l], so each load is coalesced and all lanes walk
 // their CpGs in lock-step with (almost) equal trip counts.  Because the region is
-// the same for the whole warp, the q(w) record U[m] is a broadcast operand, and the
-// per-pair record is stored component-major, stats[slice][j][lane], so both the sweep
-// (writes g, reads H^T H) and the contraction (reads everything) see 256-byte rows.
+// the same for the whole warp, the q(w) record U[m] is a broadcast operand.  The per-pair
+// records of a slice are stored in groups of four lanes,
+//     stats[slice][lane / 4][j][lane % 4]          (j = record component, R of them),
+// which is exactly the B-operand tile order of the tensor-core contraction (4 pairs x 8
+// components = 32 consecutive doubles), while the sweep still touches whole 32-byte
+// sectors when lane l reads or writes component j of its own pair.
 //
 // Included from melissa.cu inside its anonymous namespace.
 #pragma once
@@ -43,7 +46,7 @@ struct Sliced {
     int32_t *blk_cells = nullptr;         // [NB*Tn] global cell index of each block position, -1 = none
     int64_t *reg_slice_ptr = nullptr;     // [M + 1]
     int32_t *reg_slice = nullptr;         // [S]
-    double *stats = nullptr;              // [S][R][32]
+    double *stats = nullptr;              // [S][8][R][4]
     double *mills_tab = nullptr;          // [MILLS_N]
     double2 *rbf_tab = nullptr;           // [rt.n_entries] (E(u0), B(u0))
     RbfTab rt{};
@@ -268,11 +271,11 @@ __global__ void hh_sliced_kernel(const double *__restrict__ x_sell, const int64_
 #pragma unroll
             for (int c = a; c < D; ++c) hh[q++] += h[a] * h[c];
     }
-    double *rec = stats + s * R * 32 + lane;
+    double *rec = stats + s * R * 32 + (lane >> 2) * (R * 4) + (lane & 3);      // see stats layout above
 #pragma unroll
-    for (int d = 0; d < D; ++d) rec[d * 32] = 0.0;
+    for (int d = 0; d < D; ++d) rec[d * 4] = 0.0;
 #pragma unroll
-    for (int q = 0; q < T; ++q) rec[(D + q) * 32] = hh[q];
+    for (int q = 0; q < T; ++q) rec[(D + q) * 4] = hh[q];
 }
 
 // Rare path of the sweep's inner loop (x outside the table, |s mu| >= 8): plain exp / erfcx
@@ -387,10 +390,10 @@ __global__ void __launch_bounds__(256, SWEEP_MINB) sweep_v2_kernel(SweepV2Args a
 #pragma unroll
         for (int u = 0; u < XU; ++u) xa[u] = u < L ? xrow[u * 32] : 0.0;
         uint32_t yw = a.ybits[yb + lane];
-        double *rec = a.stats + s * (R * 32) + lane;
+        double *rec = a.stats + s * (R * 32) + (lane >> 2) * (R * 4) + (lane & 3);
         double hh[T];
 #pragma unroll
-        for (int q = 0; q < T; ++q) hh[q] = rec[(D + q) * 32];
+        for (int q = 0; q < T; ++q) hh[q] = rec[(D + q) * 4];
         __syncwarp();
         for (int i = lane; i < K * R; i += 32) my_u[i] = a.U[(int64_t)m * K * R + i];
         __syncwarp();
@@ -465,7 +468,7 @@ __global__ void __launch_bounds__(256, SWEEP_MINB) sweep_v2_kernel(SweepV2Args a
             yw = ywn;
         }
 #pragma unroll
-        for (int d = 0; d < D; ++d) rec[d * 32] = g[d];
+        for (int d = 0; d < D; ++d) rec[d * 4] = g[d];
         if (valid) {
             for (int k = 0; k < K; ++k) {
                 const double *u = my_u + k * R;
@@ -520,13 +523,13 @@ contract_v2_kernel(const int64_t *__restrict__ reg_slice_ptr, const int32_t *__r
                 const int64_t sb = __shfl_sync(0xffffffffu, my_s, has_b ? it + 1 : it);
                 const int cell_a = lane_cell[sa * 32 + lane];
                 const int cell_b = has_b ? lane_cell[sb * 32 + lane] : -1;
-                const double *rec_a = stats + sa * ((int64_t)R * 32) + lane;
-                const double *rec_b = stats + sb * ((int64_t)R * 32) + lane;
+                const double *rec_a = stats + sa * ((int64_t)R * 32) + (lane >> 2) * (R * 4) + (lane & 3);
+                const double *rec_b = stats + sb * ((int64_t)R * 32) + (lane >> 2) * (R * 4) + (lane & 3);
                 double va[JC], vb[JC], ra[KC], rb[KC];
 #pragma unroll
                 for (int j = 0; j < JC; ++j) {
-                    va[j] = (j0 + j < R) ? rec_a[(j0 + j) * 32] : 0.0;
-                    vb[j] = (has_b && j0 + j < R) ? rec_b[(j0 + j) * 32] : 0.0;
+                    va[j] = (j0 + j < R) ? rec_a[(j0 + j) * 4] : 0.0;
+                    vb[j] = (has_b && j0 + j < R) ? rec_b[(j0 + j) * 4] : 0.0;
                 }
 #pragma unroll
                 for (int c = 0; c < KC; ++c) {
@@ -546,5 +549,87 @@ contract_v2_kernel(const int64_t *__restrict__ reg_slice_ptr, const int32_t *__r
                 const double v = warp_sum(acc[j][c]);
                 if (lane == 0 && j0 + j < R && k0 + c < K) acc_out[((int64_t)m * K + k0 + c) * R + j0 + j] = v;
             }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// Contraction on FP64 tensor cores.  For one region the r-weighted statistics are a
+// small GEMM with a long inner dimension,
+//     acc[K x R] = r^T [K x pairs] * stats [pairs x R],
+// so each warp walks its share of the region's slices and feeds them to
+// mma.sync.m8n8k4.f64 four pairs at a time: A = r^T tile (8 clusters x 4 pairs), B =
+// stats tile (4 pairs x 8 record components), C accumulates in 2 registers per tile.
+// Every stats row is read exactly once, the reduction over pairs happens inside the MMA,
+// and the register footprint (MT*NT*2 doubles) does not grow with K*R the way the
+// per-lane accumulators of contract_v2_kernel do.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void dmma_m8n8k4(double &c0, double &c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+
+template <int MT, int NT>
+__global__ void __launch_bounds__(256)
+contract_mma_kernel(const int64_t *__restrict__ reg_slice_ptr, const int32_t *__restrict__ reg_slice,
+                    const int32_t *__restrict__ lane_cell, const double *__restrict__ stats,
+                    const double *__restrict__ r, double *__restrict__ acc_out, int K, int R) {
+    extern __shared__ double s_red[];                 // [nw][MT*NT*64]
+    const int m = blockIdx.x;
+    const int nw = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int quad = lane >> 2, tid4 = lane & 3;
+    const int64_t q0 = reg_slice_ptr[m], q1 = reg_slice_ptr[m + 1];
+    double c[MT][NT][2];
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) c[mt][nt][0] = c[mt][nt][1] = 0.0;
+    // warp w takes slices q0 + w, q0 + w + nw, ...; their ids are fetched 32 at a time (one per lane)
+    for (int64_t base = q0 + warp; base < q1; base += (int64_t)nw * 32) {
+        const int64_t mine_q = base + (int64_t)lane * nw;
+        const int my_s = mine_q < q1 ? reg_slice[mine_q] : 0;
+        const int cnt = (int)min((int64_t)32, (q1 - base + nw - 1) / nw);
+        for (int it = 0; it < cnt; ++it) {
+            const int64_t s = __shfl_sync(0xffffffffu, my_s, it);
+            const int my_cell = lane_cell[s * 32 + lane];
+            const double *rec = stats + s * ((int64_t)R * 32);
+#pragma unroll
+            for (int ks = 0; ks < 8; ++ks) {
+                const int pair = 4 * ks + tid4;
+                const int cell = __shfl_sync(0xffffffffu, my_cell, pair);
+                double a[MT], b[NT];
+#pragma unroll
+                for (int mt = 0; mt < MT; ++mt) {
+                    const int cl = mt * 8 + quad;
+                    a[mt] = (cell >= 0 && cl < K) ? r[(int64_t)cell * K + cl] : 0.0;
+                }
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) {
+                    const int j = nt * 8 + quad;
+                    b[nt] = j < R ? rec[(ks * R + j) * 4 + tid4] : 0.0;   // 32 consecutive doubles per tile
+                }
+#pragma unroll
+                for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+                    for (int nt = 0; nt < NT; ++nt) dmma_m8n8k4(c[mt][nt][0], c[mt][nt][1], a[mt], b[nt]);
+            }
+        }
+    }
+    // C fragment: lane holds rows quad (cluster), columns 2*tid4 + {0,1} (component) of each tile
+    double *mine = s_red + (size_t)warp * (MT * NT * 64);
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+            mine[(mt * NT + nt) * 64 + quad * 8 + 2 * tid4] = c[mt][nt][0];
+            mine[(mt * NT + nt) * 64 + quad * 8 + 2 * tid4 + 1] = c[mt][nt][1];
+        }
+    __syncthreads();
+    for (int i = threadIdx.x; i < MT * NT * 64; i += blockDim.x) {
+        double v = 0.0;
+        for (int w = 0; w < nw; ++w) v += s_red[(size_t)w * (MT * NT * 64) + i];
+        const int tile = i >> 6, row = (i >> 3) & 7, col = i & 7;
+        const int cl = (tile / NT) * 8 + row, j = (tile % NT) * 8 + col;
+        if (cl < K && j < R) acc_out[((int64_t)m * K + cl) * R + j] = v;
     }
 }

@@ -94,7 +94,7 @@ def test_c2_encode_holdout_fit_and_imputation(c2):
     assert abs(perf["f_measure"] - float(c2["f_measure"])) < 1e-6
 
 
-@pytest.mark.parametrize("n_basis,K", [(0, 2), (1, 3), (3, 3), (4, 5), (7, 2)])
+@pytest.mark.parametrize("n_basis,K", [(0, 2), (1, 3), (3, 3), (4, 5), (7, 2), (4, 10), (2, 17)])
 def test_ragged_sparse_coverage_vs_oracle(n_basis, K):
     # low coverage => many uncovered (cell, region) pairs, ragged 1..20 CpGs per pair
     d, tr = synth.generate(48, 37, K, n_basis=n_basis, seed=11 + n_basis, sites_per_region=40,

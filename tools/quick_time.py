@@ -15,6 +15,8 @@ t0 = time.time()
 d, tr = synth.generate(N, M, K, n_basis=4, seed=1)
 t_gen = time.time() - t0
 import os
+if os.environ.get('MELISSA_CMMA'):
+    mb.set_option('contract_mma', int(os.environ['MELISSA_CMMA']))
 if os.environ.get('MELISSA_TN'):
     mb.set_option('cell_block', int(os.environ['MELISSA_TN']))
 t0 = time.time()
