@@ -173,7 +173,7 @@ def main():
     t_gen = time.time() - t0
     P_loc, nnz_loc = int(data_t["pair_cell"].shape[0]), int(data_t["x"].shape[0])
     t0 = time.time()
-    eng = mb.Engine(data_t, tr["basis"], device=local_rank, allow_empty_regions=world > 1)
+    eng = mb.Engine(data_t, tr["basis"], device=local_rank, allow_empty_regions=world > 1, K_hint=K)
     t_pack = time.time() - t0
     delta_0 = np.full(K, 0.51)
     eng.begin(K, tr["w0"], delta_0, n_cells_total=wl["N"])
@@ -283,7 +283,7 @@ def main():
             torch.cuda.empty_cache()
             sync()
             t0 = time.perf_counter()
-            eng2 = mb.Engine(hd, tr["basis"], device=local_rank, allow_empty_regions=world > 1)
+            eng2 = mb.Engine(hd, tr["basis"], device=local_rank, allow_empty_regions=world > 1, K_hint=K)
             if group is None:
                 out = eng2.run(K, tr["w0"], delta_0, vb_max_iter=steps + 1, epsilon_conv=0.0, lb_every=LB_EVERY)
             else:

@@ -92,7 +92,10 @@ int melissa_pack_device(int32_t n_cells, int32_t n_regions, int64_t n_pairs,
 /*
  * Library-wide tuning knobs, read by the next melissa_pack*.  No counterpart in the
  * reference.
- *   "cell_block"  cells per block of the sliced layout (default 128)
+ *   "cell_block"  cells per block of the sliced layout; 0 (default) = chosen from
+ *                 "clusters_hint" so that the sweep keeps three CTAs per SM
+ *   "clusters_hint" the K the next fit will most likely use (default 4); only a
+ *                 performance hint, any K works with any layout
  *   "sliced"      -1 = use the sliced layout whenever the RBF centres are equally
  *                 spaced (default), 0 = always the flat cell-major layout, 1 = require
  *                 the sliced layout (pack fails if it cannot be used)

@@ -597,7 +597,8 @@ __global__ void impute_kernel(const int64_t *__restrict__ pair_ptr, const int32_
 #include "sliced.cuh"
 
 // library-wide options (melissa_set_option)
-int g_opt_cell_block = 128;
+int g_opt_cell_block = 0;     // 0 = derive from g_opt_clusters_hint
+int g_opt_clusters_hint = 4;
 int g_opt_sliced = -1;   // -1 auto, 0 never, 1 require
 
 void prof_begin(melissa_handle *h, int id) {
@@ -804,7 +805,16 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
     const int64_t P = h->P;
     Sliced *sl = new Sliced();
     h->sl = sl;
-    sl->Tn = std::max(1, g_opt_cell_block);
+    if (g_opt_cell_block > 0) {
+        sl->Tn = g_opt_cell_block;
+    } else {
+        // Largest multiple of 32 cells whose per-warp E-step sums (Tn x K doubles, 8 warps per CTA) still let
+        // three CTAs share an SM next to the two function tables: occupancy matters more to the sweep than
+        // the padding a smaller sorting window costs (measured at K = 4 and K = 10).
+        const int K = std::max(1, g_opt_clusters_hint), R = h->R;
+        const int budget = (75 * 1024 - 26 * 1024) / 8 / 8 - K * R;      // doubles per warp left for the sums
+        sl->Tn = std::max(32, std::min(128, (budget / K) / 32 * 32));
+    }
     const int Tn = sl->Tn;
     sl->NB = (N + Tn - 1) / Tn;
     for (int64_t p = 0; p < P; ++p)
@@ -1229,8 +1239,13 @@ int melissa_pack_device(int32_t n_cells, int32_t n_regions, int64_t n_pairs, con
 int melissa_set_option(const char *key, int64_t value) {
     if (!key) return fail(MELISSA_ERR_ARG, "key is NULL");
     if (!std::strcmp(key, "cell_block")) {
-        if (value < 1 || value > 4096) return fail(MELISSA_ERR_ARG, "cell_block must be in 1..4096");
+        if (value < 0 || value > 4096) return fail(MELISSA_ERR_ARG, "cell_block must be in 0..4096");
         g_opt_cell_block = (int)value;
+        return MELISSA_OK;
+    }
+    if (!std::strcmp(key, "clusters_hint")) {
+        if (value < 1 || value > 64) return fail(MELISSA_ERR_ARG, "clusters_hint must be in 1..64");
+        g_opt_clusters_hint = (int)value;
         return MELISSA_OK;
     }
     if (!std::strcmp(key, "contract_mma")) {

@@ -198,7 +198,7 @@ __device__ __forceinline__ bool eval_basis_fast(double x, const RbfTab &rt, cons
     return bad;
 }
 
-__device__ __forceinline__ double trunc_mean_fast(double t, const double *__restrict__ tab, bool &bad) {
+__device__ __forceinline__ double trunc_mean_fast(double t, const double *__restrict__ tab, bool &bad, double &R_out) {
     bad = !(fabs(t) < 7.99);
     const double v = fma(t, (double)MILLS_SP, MAGIC);
     const int i = min(max(__double2loint(v), -MILLS_HALF), MILLS_HALF);
@@ -217,6 +217,7 @@ __device__ __forceinline__ double trunc_mean_fast(double t, const double *__rest
     R = fma(d, R, c2);
     R = fma(d, R, c1);
     R = fma(d, R, R0);
+    R_out = R;
     return t + __drcp_rn(R);
 }
 
@@ -438,7 +439,8 @@ __global__ void __launch_bounds__(256, SWEEP_MINB) sweep_v2_kernel(SweepV2Args a
                 for (int d = 1; d < D; ++d) mu = fma(h[d], wbar[d], mu);
                 double t = __hiloint2double(__double2hiint(mu) ^ sflip, __double2loint(mu));
                 bool bad_t;
-                double G = trunc_mean_fast(t, s_mills, bad_t);
+                double Rt;
+                double G = trunc_mean_fast(t, s_mills, bad_t, Rt);
                 if (__any_sync(0xffffffffu, (bad || bad_t) && live)) {     // never taken on sane data
                     if (bad || bad_t) {
                         WBar<D> wb;
@@ -458,7 +460,11 @@ __global__ void __launch_bounds__(256, SWEEP_MINB) sweep_v2_kernel(SweepV2Args a
                 for (int d = 1; d < D; ++d) g[d] = fma(h[d], Ez, g[d]);
                 if (WITH_LB) {
                     if (live) {
-                        lb_local += 0.5 * mu * mu + loglik_term(mu, ybit != 0);
+                        // log(Phi(s mu) + 1e-10): both branches of R/melissa_vb.R:471-472 reduce to it, and
+                        // Phi = R * phi with the R the E[z] evaluation just produced (one exp + one log)
+                        const double ll = (bad || bad_t) ? loglik_term(mu, ybit != 0)
+                                                         : log(fma(Rt, 0.39894228040143267794 * exp(-0.5 * t * t), 1e-10));
+                        lb_local += 0.5 * mu * mu + ll;
                         if (t < -5.0) wrong_side += 1.0;
                     }
                 }

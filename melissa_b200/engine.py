@@ -31,8 +31,10 @@ class Engine:
     every method is one call into libmelissa_b200.so.
     """
 
-    def __init__(self, data, basis: dict, device: int = 0, allow_empty_regions: bool = False):
+    def __init__(self, data, basis: dict, device: int = 0, allow_empty_regions: bool = False, K_hint=None):
         lib = _lib.load()
+        if K_hint is not None:                  # lets the packer size its cell blocks for this K
+            _lib.check(lib.melissa_set_option(b"clusters_hint", int(min(64, max(1, K_hint)))))
         if basis.get("kind", "rbf") != "rbf":
             raise ValueError("only RBF basis objects are supported")
         self.lib = lib

@@ -137,7 +137,7 @@ def melissa(X, K=3, basis=None, delta_0=None, w=None, alpha_0=.5, beta_0=None, v
     if delta_0 is None:
         delta_0 = np.full(K, .5) + rng.beta(1e-1, 1e1, size=K)      # :110-112
     delta_0 = np.asarray(delta_0, np.float64)
-    with Engine(data, basis, device=device) as eng:
+    with Engine(data, basis, device=device, K_hint=K) as eng:
         if w is None:
             from .init import initial_w
             optimal_w = initial_w(eng, data, basis, K, delta_0, alpha_0, beta_0, epsilon_conv, is_kmeans,

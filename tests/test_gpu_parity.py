@@ -31,7 +31,7 @@ def layout(request):
         mb.set_option("cell_block", int(request.param.split("block")[1]))
     yield request.param
     mb.set_option("sliced", -1)
-    mb.set_option("cell_block", 128)
+    mb.set_option("cell_block", 0)
 
 
 def _engine(d, basis, **kw):

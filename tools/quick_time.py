@@ -20,7 +20,7 @@ if os.environ.get('MELISSA_CMMA'):
 if os.environ.get('MELISSA_TN'):
     mb.set_option('cell_block', int(os.environ['MELISSA_TN']))
 t0 = time.time()
-eng = mb.Engine(d, tr["basis"])
+eng = mb.Engine(d, tr["basis"], K_hint=K)
 t_pack = time.time() - t0
 eng.begin(K, tr["w0"], np.full(K, 0.51))
 ev = lambda: torch.cuda.Event(enable_timing=True)
