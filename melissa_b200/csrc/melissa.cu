@@ -23,10 +23,12 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <mutex>
 #include <thread>
+#include <chrono>
 #include <string>
 #include <vector>
 
@@ -596,6 +598,18 @@ __global__ void impute_kernel(const int64_t *__restrict__ pair_ptr, const int32_
 
 #include "sliced.cuh"
 
+struct StageTimer {       // MELISSA_PACK_TIMING=1 prints where melissa_pack spends its time
+    bool on = std::getenv("MELISSA_PACK_TIMING") != nullptr;
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    void lap(const char *what) {
+        if (!on) return;
+        cudaDeviceSynchronize();
+        const auto t1 = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[melissa_pack] %-28s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
+    }
+};
+
 // library-wide options (melissa_set_option)
 int g_opt_cell_block = 0;     // 0 = derive from g_opt_clusters_hint
 int g_opt_clusters_hint = 4;
@@ -805,6 +819,7 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
     const int64_t P = h->P;
     Sliced *sl = new Sliced();
     h->sl = sl;
+    StageTimer tm;
     if (g_opt_cell_block > 0) {
         sl->Tn = g_opt_cell_block;
     } else {
@@ -817,12 +832,9 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
     }
     const int Tn = sl->Tn;
     sl->NB = (N + Tn - 1) / Tn;
-    for (int64_t p = 0; p < P; ++p)
-        if (pair_ptr[p + 1] - pair_ptr[p] > 65535)
-            return fail(MELISSA_ERR_ARG, "pair %lld has more than 65535 CpGs", (long long)p);
     std::vector<int64_t> cell_ptr((size_t)N + 1, 0);
-    for (int64_t p = 0; p < P; ++p) cell_ptr[(size_t)pair_cell[p] + 1]++;
-    for (int n = 0; n < N; ++n) cell_ptr[(size_t)n + 1] += cell_ptr[n];
+    for (int n = 0; n <= N; ++n)       // pair_cell is sorted: N + 1 binary searches instead of a pass over P
+        cell_ptr[(size_t)n] = std::lower_bound(pair_cell, pair_cell + P, (int32_t)n) - pair_cell;
     // ---- blocks hold cells of similar coverage (sorted by CpG count), so that the pairs a slice groups
     //      have similar lengths and little of the lock-step loop is padding
     std::vector<int32_t> blk_cells((size_t)sl->NB * Tn, -1);
@@ -835,6 +847,7 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
         });
         for (int n = 0; n < N; ++n) blk_cells[(size_t)n] = order[(size_t)n];
     }
+    tm.lap("cell order");
     // ---- slices, built by a few host threads over ranges of cell blocks
     int nthr = (int)std::min<int64_t>(std::max(1u, std::thread::hardware_concurrency()), 16);
     nthr = std::max(1, std::min(nthr, sl->NB));
@@ -851,38 +864,58 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
         }
         for (auto &t : th) t.join();
     }
-    SliceBuild all;
-    for (auto &pt : parts) {
-        all.slice_region.insert(all.slice_region.end(), pt.slice_region.begin(), pt.slice_region.end());
-        all.slice_len.insert(all.slice_len.end(), pt.slice_len.begin(), pt.slice_len.end());
-        all.slice_cb.insert(all.slice_cb.end(), pt.slice_cb.begin(), pt.slice_cb.end());
-        all.lane_cell.insert(all.lane_cell.end(), pt.lane_cell.begin(), pt.lane_cell.end());
-        all.lane_pair.insert(all.lane_pair.end(), pt.lane_pair.begin(), pt.lane_pair.end());
-        all.lane_meta.insert(all.lane_meta.end(), pt.lane_meta.begin(), pt.lane_meta.end());
-        all.lane_src.insert(all.lane_src.end(), pt.lane_src.begin(), pt.lane_src.end());
-        pt = SliceBuild();
-    }
-    const int64_t S = (int64_t)all.slice_region.size();
+    tm.lap("build slices (threads)");
+    // the per-thread pieces are never concatenated on the host: they go to the device piece by piece
+    std::vector<int64_t> soff((size_t)nthr + 1, 0);
+    for (int t = 0; t < nthr; ++t) soff[(size_t)t + 1] = soff[(size_t)t] + (int64_t)parts[(size_t)t].slice_region.size();
+    const int64_t S = soff[(size_t)nthr];
     sl->S = S;
     if (S >= (int64_t)std::numeric_limits<int32_t>::max()) return fail(MELISSA_ERR_ARG, "too many slices");
-    std::vector<int64_t> xbase((size_t)S), ybase((size_t)S);
-    int64_t xo = 0, yo = 0;
-    for (int64_t q = 0; q < S; ++q) {
-        xbase[(size_t)q] = xo;
-        ybase[(size_t)q] = yo;
-        xo += (int64_t)all.slice_len[(size_t)q] * 32;
-        yo += (int64_t)((all.slice_len[(size_t)q] + 31) / 32) * 32;
+    // x / y offsets of every slice: local prefix sums per piece, then the piece's base
+    std::vector<std::vector<int64_t>> xbase((size_t)nthr), ybase((size_t)nthr);
+    std::vector<int64_t> xtot((size_t)nthr + 1, 0), ytot((size_t)nthr + 1, 0);
+    {
+        std::vector<std::thread> th;
+        for (int t = 0; t < nthr; ++t)
+            th.emplace_back([&, t]() {
+                const auto &len = parts[(size_t)t].slice_len;
+                xbase[(size_t)t].resize(len.size());
+                ybase[(size_t)t].resize(len.size());
+                int64_t xo = 0, yo = 0;
+                for (size_t q = 0; q < len.size(); ++q) {
+                    xbase[(size_t)t][q] = xo;
+                    ybase[(size_t)t][q] = yo;
+                    xo += (int64_t)len[q] * 32;
+                    yo += (int64_t)((len[q] + 31) / 32) * 32;
+                }
+                xtot[(size_t)t + 1] = xo;
+                ytot[(size_t)t + 1] = yo;
+            });
+        for (auto &t : th) t.join();
+        for (int t = 0; t < nthr; ++t) { xtot[(size_t)t + 1] += xtot[(size_t)t]; ytot[(size_t)t + 1] += ytot[(size_t)t]; }
+        th.clear();
+        for (int t = 0; t < nthr; ++t)
+            th.emplace_back([&, t]() {
+                for (auto &v : xbase[(size_t)t]) v += xtot[(size_t)t];
+                for (auto &v : ybase[(size_t)t]) v += ytot[(size_t)t];
+            });
+        for (auto &t : th) t.join();
     }
-    sl->x_len = xo;
-    sl->y_len = yo;
+    sl->x_len = xtot[(size_t)nthr];
+    sl->y_len = ytot[(size_t)nthr];
+    tm.lap("offsets");
     // ---- region-major list of slices
     std::vector<int64_t> reg_slice_ptr((size_t)M + 1, 0);
     std::vector<int32_t> reg_slice((size_t)S);
-    for (int64_t q = 0; q < S; ++q) reg_slice_ptr[(size_t)all.slice_region[(size_t)q] + 1]++;
+    for (int t = 0; t < nthr; ++t)
+        for (int32_t m : parts[(size_t)t].slice_region) reg_slice_ptr[(size_t)m + 1]++;
     for (int m = 0; m < M; ++m) reg_slice_ptr[(size_t)m + 1] += reg_slice_ptr[m];
     {
         std::vector<int64_t> cur(reg_slice_ptr.begin(), reg_slice_ptr.end() - 1);
-        for (int64_t q = 0; q < S; ++q) reg_slice[(size_t)cur[all.slice_region[(size_t)q]]++] = (int32_t)q;
+        for (int t = 0; t < nthr; ++t) {
+            const auto &reg = parts[(size_t)t].slice_region;
+            for (size_t q = 0; q < reg.size(); ++q) reg_slice[(size_t)cur[reg[q]]++] = (int32_t)(soff[(size_t)t] + (int64_t)q);
+        }
     }
     // ---- RBF table (host exp) and the Mills table (device erfcx)
     const BasisDev &b = h->basis;
@@ -911,23 +944,48 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
         rt.n_entries = 1;
         rbf_tab.assign(1, make_double2(1.0, 1.0));
     }
-    // ---- upload
+    tm.lap("region index + tables");
+    // ---- upload, piece by piece
     int rc;
     int64_t *d_src = nullptr;
-    if ((rc = upload(&sl->slice_xbase, xbase)) || (rc = upload(&sl->slice_ybase, ybase)) ||
-        (rc = upload(&sl->slice_len, all.slice_len)) || (rc = upload(&sl->slice_region, all.slice_region)) ||
-        (rc = upload(&sl->slice_cb, all.slice_cb)) || (rc = upload(&sl->blk_cells, blk_cells)) ||
-        (rc = upload(&sl->lane_cell, all.lane_cell)) || (rc = upload(&sl->lane_meta, all.lane_meta)) ||
-        (rc = upload(&sl->reg_slice_ptr, reg_slice_ptr)) ||
-        (rc = upload(&sl->reg_slice, reg_slice)) || (rc = upload(&sl->rbf_tab, rbf_tab)) ||
-        (rc = upload(&d_src, all.lane_src)))
+    if ((rc = dev_alloc(&sl->slice_xbase, S)) || (rc = dev_alloc(&sl->slice_ybase, S)) ||
+        (rc = dev_alloc(&sl->slice_len, S)) || (rc = dev_alloc(&sl->slice_region, S)) ||
+        (rc = dev_alloc(&sl->slice_cb, S)) || (rc = dev_alloc(&sl->lane_cell, S * 32)) ||
+        (rc = dev_alloc(&sl->lane_meta, S * 32)) || (rc = dev_alloc(&d_src, S * 32)) ||
+        (rc = upload(&sl->blk_cells, blk_cells)) || (rc = upload(&sl->reg_slice_ptr, reg_slice_ptr)) ||
+        (rc = upload(&sl->reg_slice, reg_slice)) || (rc = upload(&sl->rbf_tab, rbf_tab))) {
+        cudaFree(d_src);
         return rc;
+    }
+    for (int t = 0; t < nthr; ++t) {
+        const SliceBuild &pt = parts[(size_t)t];
+        const int64_t o = soff[(size_t)t];
+        const size_t n = pt.slice_region.size();
+        if (!n) continue;
+#define PUT(dst, vec, mul, Tp)                                                                              \
+        if (cudaMemcpyAsync(dst + o * mul, vec.data(), n * mul * sizeof(Tp), cudaMemcpyHostToDevice, nullptr) != \
+            cudaSuccess) {                                                                                    \
+            cudaFree(d_src);                                                                                  \
+            return fail(MELISSA_ERR_CUDA, "upload of the slice index failed: %s",                             \
+                        cudaGetErrorString(cudaGetLastError()));                                              \
+        }
+        PUT(sl->slice_xbase, xbase[(size_t)t], 1, int64_t)
+        PUT(sl->slice_ybase, ybase[(size_t)t], 1, int64_t)
+        PUT(sl->slice_len, pt.slice_len, 1, int32_t)
+        PUT(sl->slice_region, pt.slice_region, 1, int32_t)
+        PUT(sl->slice_cb, pt.slice_cb, 1, int32_t)
+        PUT(sl->lane_cell, pt.lane_cell, 32, int32_t)
+        PUT(sl->lane_meta, pt.lane_meta, 32, int32_t)
+        PUT(d_src, pt.lane_src, 32, int64_t)
+#undef PUT
+    }
     if ((rc = dev_alloc(&sl->x_sell, sl->x_len)) || (rc = dev_alloc(&sl->ybits, sl->y_len)) ||
         (rc = dev_alloc(&sl->stats, S * h->R * 32)) || (rc = dev_alloc(&sl->mills_tab, MILLS_N)) ||
         (rc = dev_alloc(&sl->slice_counter, 1))) {
         cudaFree(d_src);
         return rc;
     }
+    tm.lap("upload index arrays");
     const int grid = (int)((S * 32 + 255) / 256);
     sell_fill_kernel<<<grid, 256>>>(h->x, h->y, d_src, sl->lane_meta, sl->slice_xbase, sl->slice_ybase, sl->slice_len,
                                     sl->x_sell, sl->ybits, S);
@@ -944,7 +1002,9 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
     const cudaError_t e = cudaDeviceSynchronize();
     cudaFree(d_src);
     if (e != cudaSuccess) return fail(MELISSA_ERR_CUDA, "sliced layout build failed: %s", cudaGetErrorString(e));
-    sl->lane_pair = std::move(all.lane_pair);
+    tm.lap("fill + HtH kernels");
+    sl->lane_pair.resize((size_t)nthr);
+    for (int t = 0; t < nthr; ++t) sl->lane_pair[(size_t)t] = std::move(parts[(size_t)t].lane_pair);
     sl->on = true;
     return MELISSA_OK;
 }
@@ -1075,6 +1135,7 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
                      double gamma, int32_t device, int32_t allow_empty_regions, bool on_device,
                      melissa_handle **out) {
     if (!out) return fail(MELISSA_ERR_ARG, "out is NULL");
+    StageTimer tm_pack;
     const int64_t *pair_ptr = pair_ptr_in;
     const int32_t *pair_cell = pair_cell_in, *pair_region = pair_region_in;
     std::vector<int64_t> host_ptr;
@@ -1103,39 +1164,66 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
     if (n_basis < 0 || n_basis + 1 > MAX_D || (n_basis > 0 && !mus))
         return fail(MELISSA_ERR_ARG, "basis$M must be in 0..%d", MAX_D - 1);
     if (!(gamma > 0.0) && n_basis > 0) return fail(MELISSA_ERR_ARG, "basis$gamma must be positive");
+    tm_pack.lap("index lists to host");
     // ---- validate the pair list (host) and build the region-major index
     const int64_t P = n_pairs;
     if (pair_ptr[0] != 0) return fail(MELISSA_ERR_ARG, "pair_ptr[0] must be 0");
     std::vector<int64_t> reg_cnt((size_t)n_regions + 1, 0);
-    int32_t prev_cell = -1, prev_region = -1;
-    int32_t cells_seen = 0;
-    for (int64_t p = 0; p < P; ++p) {
-        const int32_t n = pair_cell[p], m = pair_region[p];
-        if (n < 0 || n >= n_cells || m < 0 || m >= n_regions)
-            return fail(MELISSA_ERR_ARG, "pair %lld: cell/region index out of range", (long long)p);
-        if (n < prev_cell) return fail(MELISSA_ERR_ARG, "pairs must be cell-major (pair %lld)", (long long)p);
-        if (n != prev_cell) {
-            if (n != prev_cell + 1)
-                return fail(MELISSA_ERR_ARG, "cell %d: No coverage across all regions. This cell should be discarded!",
-                            prev_cell + 1);
-            ++cells_seen;
-            prev_region = -1;
+    {
+        // every rule relates pair p to pair p-1 only, so chunks are checked by separate host threads;
+        // the failure with the lowest pair index is the one reported
+        int nthr = (int)std::min<int64_t>(std::max(1u, std::thread::hardware_concurrency()), 16);
+        if (P < 400000) nthr = 1;
+        struct Bad { int64_t p = -1; int code = 0; };
+        std::vector<Bad> bad((size_t)nthr);
+        std::vector<std::vector<int64_t>> cnt((size_t)nthr);
+        auto work = [&](int t) {
+            const int64_t lo = P * t / nthr, hi = P * (t + 1) / nthr;
+            std::vector<int64_t> &c = cnt[(size_t)t];
+            c.assign((size_t)n_regions, 0);
+            for (int64_t p = lo; p < hi; ++p) {
+                const int32_t n = pair_cell[p], m = pair_region[p];
+                int code = 0;
+                if (n < 0 || n >= n_cells || m < 0 || m >= n_regions) code = 1;
+                else {
+                    const int32_t pn = p ? pair_cell[p - 1] : -1, pm = p ? pair_region[p - 1] : -1;
+                    if (n < pn) code = 2;
+                    else if (n > pn + 1) code = 3;
+                    else if (n == pn && m <= pm) code = 4;
+                    else if (pair_ptr[p + 1] <= pair_ptr[p]) code = 5;
+                    else if (pair_ptr[p + 1] - pair_ptr[p] > 65535) code = 6;
+                }
+                if (code) { bad[(size_t)t].p = p; bad[(size_t)t].code = code; return; }
+                c[(size_t)m]++;
+            }
+        };
+        if (nthr == 1) work(0);
+        else {
+            std::vector<std::thread> th;
+            for (int t = 0; t < nthr; ++t) th.emplace_back(work, t);
+            for (auto &t : th) t.join();
         }
-        if (m <= prev_region)
-            return fail(MELISSA_ERR_ARG, "regions must be strictly increasing inside a cell (pair %lld)", (long long)p);
-        if (pair_ptr[p + 1] <= pair_ptr[p])
-            return fail(MELISSA_ERR_ARG, "pair %lld has no CpG", (long long)p);
-        prev_cell = n;
-        prev_region = m;
-        reg_cnt[(size_t)m + 1]++;
+        for (int t = 0; t < nthr; ++t) {
+            const Bad &b = bad[(size_t)t];
+            if (b.p < 0) continue;
+            const long long p = (long long)b.p;
+            switch (b.code) {
+                case 1: return fail(MELISSA_ERR_ARG, "pair %lld: cell/region index out of range", p);
+                case 2: return fail(MELISSA_ERR_ARG, "pairs must be cell-major (pair %lld)", p);
+                case 3: return fail(MELISSA_ERR_ARG, "cell %d: No coverage across all regions. This cell should be discarded!",
+                                    (b.p ? pair_cell[b.p - 1] : -1) + 1);
+                case 4: return fail(MELISSA_ERR_ARG, "regions must be strictly increasing inside a cell (pair %lld)", p);
+                case 5: return fail(MELISSA_ERR_ARG, "pair %lld has no CpG", p);
+                default: return fail(MELISSA_ERR_ARG, "pair %lld has more than 65535 CpGs", p);
+            }
+        }
+        if (pair_cell[P - 1] != n_cells - 1)
+            return fail(MELISSA_ERR_ARG, "cell %d: No coverage across all regions. This cell should be discarded!",
+                        pair_cell[P - 1] + 1);
+        for (int t = 0; t < nthr; ++t)
+            for (int32_t m = 0; m < n_regions; ++m) reg_cnt[(size_t)m + 1] += cnt[(size_t)t][(size_t)m];
     }
-    if (cells_seen != n_cells)
-        return fail(MELISSA_ERR_ARG, "cell %d: No coverage across all regions. This cell should be discarded!", cells_seen);
     const int64_t nnz = pair_ptr[P];
-    if (!on_device) {
-        for (int64_t i = 0; i < nnz; ++i)
-            if (y[i] > 1) return fail(MELISSA_ERR_ARG, "methylation state y[%lld] is not 0/1", (long long)i);
-    }
     if (!allow_empty_regions)
         for (int32_t m = 0; m < n_regions; ++m)
             if (reg_cnt[(size_t)m + 1] == 0)
@@ -1158,6 +1246,7 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
             reg_cell[(size_t)q] = pair_cell[p];
         }
     }
+    tm_pack.lap("validate");
     // ---- device side
     CU(cudaSetDevice(device));
     melissa_handle *h = new melissa_handle();
@@ -1169,7 +1258,8 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) h->sm_count = prop.multiProcessorCount;
     int rc = MELISSA_OK;
-    auto bail = [&](int code) { melissa_free(h); return code; };
+    unsigned long long *bad_y = nullptr;
+    auto bail = [&](int code) { cudaFree(bad_y); melissa_free(h); return code; };
 #define H2D(dst, src, n, Tp)                                                                          \
     if (cudaMemcpyAsync(dst, src, (size_t)(n) * sizeof(Tp), cudaMemcpyDefault, nullptr) != cudaSuccess)    \
         return bail(fail(MELISSA_ERR_CUDA, "copy of " #src " failed: %s", cudaGetErrorString(cudaGetLastError())))
@@ -1177,15 +1267,12 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
     if ((rc = dev_alloc(&h->y, nnz))) return bail(rc);
     H2D(h->x, x, nnz, double);
     H2D(h->y, y, nnz, uint8_t);
-    if (on_device) {
-        unsigned long long *bad = nullptr, bad_h = 0;
-        if ((rc = dev_alloc(&bad, 1))) return bail(rc);
-        cudaMemsetAsync(bad, 0, sizeof(unsigned long long), nullptr);
-        count_bad_y_kernel<<<grid_for(nnz, 256, h->sm_count, 8), 256>>>(h->y, nnz, bad);
-        cudaMemcpy(&bad_h, bad, sizeof bad_h, cudaMemcpyDeviceToHost);
-        cudaFree(bad);
-        if (bad_h) return bail(fail(MELISSA_ERR_ARG, "%llu methylation states are not 0/1", bad_h));
-    }
+    // y is checked on the device once it has arrived; the verdict is read after the host has built the
+    // layout, so that (from pinned memory) the copy and the host work overlap
+    if ((rc = dev_alloc(&bad_y, 1))) return bail(rc);
+    cudaMemsetAsync(bad_y, 0, sizeof(unsigned long long), nullptr);
+    count_bad_y_kernel<<<grid_for(nnz, 256, h->sm_count, 8), 256>>>(h->y, nnz, bad_y);
+    tm_pack.lap("x / y to device");
     if (use_sliced) {
         // v2: re-lay the observations into region slices, then drop the flat copies
         if ((rc = build_sliced(h, pair_ptr, pair_cell, pair_region))) return bail(rc);
@@ -1214,6 +1301,14 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
         h->launches++;
     }
 #undef H2D
+    {
+        unsigned long long bad_h = 0;
+        const cudaError_t e = cudaMemcpy(&bad_h, bad_y, sizeof bad_h, cudaMemcpyDeviceToHost);
+        cudaFree(bad_y);
+        bad_y = nullptr;
+        if (e != cudaSuccess) return bail(fail(MELISSA_ERR_CUDA, "pack failed: %s", cudaGetErrorString(e)));
+        if (bad_h) return bail(fail(MELISSA_ERR_ARG, "%llu methylation states are not 0/1", bad_h));
+    }
     if (cudaDeviceSynchronize() != cudaSuccess)
         return bail(fail(MELISSA_ERR_CUDA, "pack failed: %s", cudaGetErrorString(cudaGetLastError())));
     *out = h;
@@ -1500,13 +1595,15 @@ int melissa_vb_fetch_HtEz(melissa_handle *h, double *out) {
         const size_t rec = (size_t)h->R * 32;
         std::vector<double> buf((size_t)sl->S * rec);
         CU(cudaMemcpy(buf.data(), sl->stats, buf.size() * sizeof(double), cudaMemcpyDeviceToHost));
-        for (int64_t q = 0; q < sl->S; ++q)
-            for (int l = 0; l < 32; ++l) {
-                const int32_t p = sl->lane_pair[(size_t)q * 32 + l];
-                if (p < 0) continue;
-                for (int d = 0; d < h->D; ++d)
-                    out[(size_t)p * h->D + d] = buf[(size_t)q * rec + ((size_t)(l >> 2) * h->R + d) * 4 + (l & 3)];
-            }
+        int64_t q = 0;
+        for (const auto &piece : sl->lane_pair)
+            for (size_t i = 0; i < piece.size(); i += 32, ++q)
+                for (int l = 0; l < 32; ++l) {
+                    const int32_t p = piece[i + l];
+                    if (p < 0) continue;
+                    for (int d = 0; d < h->D; ++d)
+                        out[(size_t)p * h->D + d] = buf[(size_t)q * rec + ((size_t)(l >> 2) * h->R + d) * 4 + (l & 3)];
+                }
         return MELISSA_OK;
     }
     CU(cudaMemcpy2D(out, (size_t)h->D * sizeof(double), h->stats, (size_t)h->R * sizeof(double),

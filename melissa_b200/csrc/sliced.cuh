@@ -51,7 +51,7 @@ struct Sliced {
     double2 *rbf_tab = nullptr;           // [rt.n_entries] (E(u0), B(u0))
     RbfTab rt{};
     unsigned long long *slice_counter = nullptr;   // slice dispenser of the persistent sweep
-    std::vector<int32_t> lane_pair;       // host: original pair of (slice, lane), -1 = padding
+    std::vector<std::vector<int32_t>> lane_pair;   // host, per build piece: original pair of (slice, lane), -1 = padding
 };
 
 // R(t0) = Phi(t0) / phi(t0) on the grid t0 = (i - MILLS_HALF) / MILLS_SP.
