@@ -979,12 +979,14 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
         PUT(d_src, pt.lane_src, 32, int64_t)
 #undef PUT
     }
-    if ((rc = dev_alloc(&sl->x_sell, sl->x_len)) || (rc = dev_alloc(&sl->ybits, sl->y_len)) ||
+    // + 2 prefetch groups of slack: the sweep reads one group past the end of every slice
+    if ((rc = dev_alloc(&sl->x_sell, sl->x_len + 2 * SWEEP_XU * 32)) || (rc = dev_alloc(&sl->ybits, sl->y_len)) ||
         (rc = dev_alloc(&sl->stats, S * h->R * 32)) || (rc = dev_alloc(&sl->mills_tab, MILLS_N)) ||
         (rc = dev_alloc(&sl->slice_counter, 1))) {
         cudaFree(d_src);
         return rc;
     }
+    cudaMemsetAsync(sl->x_sell + sl->x_len, 0, (size_t)2 * SWEEP_XU * 32 * sizeof(double), nullptr);
     tm.lap("upload index arrays");
     const int grid = (int)((S * 32 + 255) / 256);
     sell_fill_kernel<<<grid, 256>>>(h->x, h->y, d_src, sl->lane_meta, sl->slice_xbase, sl->slice_ybase, sl->slice_len,

@@ -279,34 +279,52 @@ __global__ void hh_sliced_kernel(const double *__restrict__ x_sell, const int64_
     for (int q = 0; q < T; ++q) rec[(D + q) * 4] = hh[q];
 }
 
-// Rare path of the sweep's inner loop (x outside the table, |s mu| >= 8): plain exp / erfcx
-// evaluation of one CpG.  Kept out of line so it costs the hot loop no registers.
+// Rare path of the sweep (some x outside the table, or |s mu| >= 8, in some lane of the slice):
+// the whole slice is redone with plain exp / erfcx evaluation, after and outside the row loop.
+// (Inlined: an out-of-line call anywhere in the kernel makes ptxas keep the hot loop's state in
+// ABI registers and spill around it -- measured 1.1 -> 1.6 ms.)
 template <int D>
-struct CpgSlow {
-    double h[D];
-    double mu, t, G;
+struct SliceSums {
+    double g[D];
+    double lb, wrong;
 };
 template <int D>
 struct WBar {
     double w[D];
 };
-#ifndef SLOW_INLINE
-#define SLOW_INLINE 1
+#ifndef SLICE_SLOW_NOINLINE
+#define SLICE_SLOW_NOINLINE 0
 #endif
-#if SLOW_INLINE
-#define SLOW_ATTR __forceinline__
+#if SLICE_SLOW_NOINLINE
+#define SLICE_SLOW_ATTR __noinline__
 #else
-#define SLOW_ATTR __noinline__
+#define SLICE_SLOW_ATTR __forceinline__
 #endif
-template <int D>
-__device__ SLOW_ATTR CpgSlow<D> cpg_slow(double x, uint32_t ybit, WBar<D> wb, const BasisDev *basis) {
-    CpgSlow<D> o;
-    eval_basis<D>(x, *basis, o.h);
-    o.mu = wb.w[0];
+template <int D, bool WITH_LB>
+__device__ SLICE_SLOW_ATTR SliceSums<D> sweep_slice_slow(const double *xrow, const uint32_t *yrow, int L, int len,
+                                                      WBar<D> wb, const BasisDev *basis) {
+    SliceSums<D> o;
 #pragma unroll
-    for (int d = 1; d < D; ++d) o.mu = fma(o.h[d], wb.w[d], o.mu);
-    o.t = ybit ? o.mu : -o.mu;
-    o.G = trunc_mean(o.t);
+    for (int d = 0; d < D; ++d) o.g[d] = 0.0;
+    o.lb = 0.0;
+    o.wrong = 0.0;
+    for (int i = 0; i < len && i < L; ++i) {
+        const bool yi = (yrow[(int64_t)(i >> 5) * 32] >> (i & 31)) & 1u;
+        double h[D];
+        eval_basis<D>(xrow[(int64_t)i * 32], *basis, h);
+        double mu = wb.w[0];
+#pragma unroll
+        for (int d = 1; d < D; ++d) mu = fma(h[d], wb.w[d], mu);
+        const double t = yi ? mu : -mu;
+        const double G = trunc_mean(t);
+        const double Ez = yi ? G : -G;
+#pragma unroll
+        for (int d = 0; d < D; ++d) o.g[d] = fma(h[d], Ez, o.g[d]);
+        if (WITH_LB) {
+            o.lb += 0.5 * mu * mu + loglik_term(mu, yi);
+            if (t < -5.0) o.wrong += 1.0;
+        }
+    }
     return o;
 }
 
@@ -389,7 +407,7 @@ __global__ void __launch_bounds__(256, SWEEP_MINB) sweep_v2_kernel(SweepV2Args a
         const double *xrow = a.x_sell + xb + lane;
         double xa[XU];
 #pragma unroll
-        for (int u = 0; u < XU; ++u) xa[u] = u < L ? xrow[u * 32] : 0.0;
+        for (int u = 0; u < XU; ++u) xa[u] = xrow[u * 32];
         uint32_t yw = a.ybits[yb + lane];
         double *rec = a.stats + s * (R * 32) + (lane >> 2) * (R * 4) + (lane & 3);
         double hh[T];
@@ -418,12 +436,17 @@ __global__ void __launch_bounds__(256, SWEEP_MINB) sweep_v2_kernel(SweepV2Args a
         double g[D];
 #pragma unroll
         for (int d = 0; d < D; ++d) g[d] = 0.0;
-        // Rows beyond L read as x = 0 and rows beyond a lane's own length are masked to
-        // E[z] = 0, so every group runs all XU rows with no trip-count test inside.
+        // Rows past a lane's own length are masked to E[z] = 0 and rows past L (read from whatever
+        // follows in x_sell, which is over-allocated by one group) are past every lane's length,
+        // so each group runs all XU rows with no trip-count test and no predicated load.
+        double lb_s = 0.0, wrong_s = 0.0;
+        bool bad_any = false;
+        const double *xp = xrow;
         for (int i0 = 0; i0 < L; i0 += XU) {
             double xnext[XU];
 #pragma unroll
-            for (int u = 0; u < XU; ++u) xnext[u] = (i0 + XU + u < L) ? xrow[(int64_t)(i0 + XU + u) * 32] : 0.0;
+            for (int u = 0; u < XU; ++u) xnext[u] = xp[(XU + u) * 32];
+            xp += XU * 32;
             uint32_t ywn = yw;
             if (((i0 + XU) & 31) == 0 && i0 + XU < L) ywn = a.ybits[yb + (int64_t)((i0 + XU) >> 5) * 32 + lane];
 #pragma unroll
@@ -433,27 +456,15 @@ __global__ void __launch_bounds__(256, SWEEP_MINB) sweep_v2_kernel(SweepV2Args a
                 const uint32_t sflip = (ybit ^ 1u) << 31;             // s = +1 for y = 1, -1 for y = 0
                 const uint32_t live = i < len ? 0xffffffffu : 0u;
                 double h[D];
-                bool bad = eval_basis_fast<D>(xa[u], a.rt, s_rbf, h);
+                const bool bad = eval_basis_fast<D>(xa[u], a.rt, s_rbf, h);
                 double mu = wbar[0];
 #pragma unroll
                 for (int d = 1; d < D; ++d) mu = fma(h[d], wbar[d], mu);
-                double t = __hiloint2double(__double2hiint(mu) ^ sflip, __double2loint(mu));
+                const double t = __hiloint2double(__double2hiint(mu) ^ sflip, __double2loint(mu));
                 bool bad_t;
                 double Rt;
-                double G = trunc_mean_fast(t, s_mills, bad_t, Rt);
-                if (__any_sync(0xffffffffu, (bad || bad_t) && live)) {     // never taken on sane data
-                    if (bad || bad_t) {
-                        WBar<D> wb;
-#pragma unroll
-                        for (int d = 0; d < D; ++d) wb.w[d] = wbar[d];
-                        const CpgSlow<D> o = cpg_slow<D>(xa[u], ybit, wb, &a.basis);
-#pragma unroll
-                        for (int d = 0; d < D; ++d) h[d] = o.h[d];
-                        mu = o.mu;
-                        t = o.t;
-                        G = o.G;
-                    }
-                }
+                const double G = trunc_mean_fast(t, s_mills, bad_t, Rt);
+                bad_any |= (bad || bad_t) && live;
                 const double Ez = __hiloint2double((__double2hiint(G) ^ sflip) & live, __double2loint(G) & live);
                 g[0] += Ez;
 #pragma unroll
@@ -462,16 +473,28 @@ __global__ void __launch_bounds__(256, SWEEP_MINB) sweep_v2_kernel(SweepV2Args a
                     if (live) {
                         // log(Phi(s mu) + 1e-10): both branches of R/melissa_vb.R:471-472 reduce to it, and
                         // Phi = R * phi with the R the E[z] evaluation just produced (one exp + one log)
-                        const double ll = (bad || bad_t) ? loglik_term(mu, ybit != 0)
-                                                         : log(fma(Rt, 0.39894228040143267794 * exp(-0.5 * t * t), 1e-10));
-                        lb_local += 0.5 * mu * mu + ll;
-                        if (t < -5.0) wrong_side += 1.0;
+                        lb_s += 0.5 * mu * mu + log(fma(Rt, 0.39894228040143267794 * exp(-0.5 * t * t), 1e-10));
+                        if (t < -5.0) wrong_s += 1.0;
                     }
                 }
             }
 #pragma unroll
             for (int u = 0; u < XU; ++u) xa[u] = xnext[u];
             yw = ywn;
+        }
+        if (__any_sync(0xffffffffu, bad_any)) {                    // never taken on sane data
+            WBar<D> wb;
+#pragma unroll
+            for (int d = 0; d < D; ++d) wb.w[d] = wbar[d];
+            const SliceSums<D> o = sweep_slice_slow<D, WITH_LB>(xrow, a.ybits + yb + lane, L, len, wb, &a.basis);
+#pragma unroll
+            for (int d = 0; d < D; ++d) g[d] = o.g[d];
+            lb_s = o.lb;
+            wrong_s = o.wrong;
+        }
+        if (WITH_LB) {
+            lb_local += lb_s;
+            wrong_side += wrong_s;
         }
 #pragma unroll
         for (int d = 0; d < D; ++d) rec[d * 4] = g[d];

@@ -196,3 +196,22 @@ def test_size_independent_properties_at_scale():
     assert mb.cluster_ari(tr["C_true"], res["r_nk"]) == 1.0
     np.testing.assert_allclose(res_p["lb"][1:], lb, rtol=1e-12)
     np.testing.assert_allclose(res_p["r_nk"][::-1], res["r_nk"], atol=1e-9)
+
+
+def test_rare_path_positions_outside_the_table_and_far_tails():
+    # x beyond [-1, 1] (outside the RBF table) and |mu| >= 8 (outside the Mills table) take the plain
+    # exp / erfcx path; the oracle is run with the cancellation-free E[z] form, since the reference's own
+    # expression returns Inf there (deviation 2)
+    K = 3
+    d, tr = synth.generate(40, 25, K, n_basis=4, seed=21, sites_per_region=60, cov_lo=0.1, cov_hi=0.4)
+    d.x[::37] *= 1.35
+    w0 = tr["w0"] * 7.0
+    delta_0 = np.full(K, 0.6)
+    ref = mo.melissa_inner(d.as_dict(), K, tr["basis"], w0, delta_0, vb_max_iter=12, mimic=False)
+    with mb.Engine(d, tr["basis"]) as eng:
+        eng.begin(K, w0, delta_0)
+        g = eng.fetch_HtEz()
+        res = eng.run(K, w0, delta_0, vb_max_iter=12)
+    assert np.isfinite(g).all()
+    np.testing.assert_allclose(res["lb"][1:], ref["lb"][1:], rtol=1e-8)
+    np.testing.assert_allclose(res["r_nk"], ref["r_nk"], atol=1e-7)
