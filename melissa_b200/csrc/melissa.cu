@@ -1051,6 +1051,7 @@ int launch_sweep_v2(melissa_handle *h, bool with_lb, bool uniform_r) {
         int per_sm = 1;                                                                                     \
         CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, block, smem));                       \
         grid = (int)std::min<int64_t>((sl->S + nw - 1) / nw, (int64_t)h->sm_count * std::max(1, per_sm));  \
+        a.chunk = std::max<int64_t>(1, std::min<int64_t>(64, sl->S / ((int64_t)grid * nw * 4)));            \
         kfn<<<grid, block, smem, h->stream>>>(a);                                                           \
     })
     if (with_lb && uniform_r) { SWEEP2(true, true) }

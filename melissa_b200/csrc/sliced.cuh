@@ -342,7 +342,7 @@ struct SweepV2Args {
     BasisDev basis;
     int K, Tn, N;
     unsigned long long *slice_counter;
-    int64_t S;
+    int64_t S, chunk;
 };
 
 // The per-CpG sweep on slices (R/melissa_vb.R:418-435 refresh + the next iteration's
@@ -372,36 +372,49 @@ __global__ void __launch_bounds__(256, SWEEP_MINB) sweep_v2_kernel(SweepV2Args a
     double *my_u = s_u + warp * K * R;
     double *my_acc = s_acc + warp * Tn * K;
     double lb_local = 0.0, wrong_side = 0.0;
-    int cur_cb = -1;
+    int cur_cb = -1, cur_m = -1;
+    // Slices are handed out in runs of `chunk` consecutive ones: a run stays inside one or two cell
+    // blocks, so the private sums are flushed once per run instead of once per slice (with ~3,500
+    // warps in flight, single slices would land every warp in a new block each time).
+    const int64_t chunk = a.chunk;
     auto claim = [&]() -> int64_t {
         unsigned long long c = 0;
-        if (lane == 0) c = atomicAdd(a.slice_counter, 1ull);
+        if (lane == 0) c = atomicAdd(a.slice_counter, (unsigned long long)chunk);
         return (int64_t)__shfl_sync(0xffffffffu, c, 0);
     };
     auto flush = [&]() {                        // private sums of block cur_cb -> log_rho, then clear
         if (cur_cb < 0) return;
         __syncwarp();
-        for (int i = lane; i < Tn * K; i += 32) {
-            const double v = my_acc[i];
-            const int cell = a.blk_cells[(int64_t)cur_cb * Tn + i / K];
-            if (cell >= 0 && v != 0.0) atomicAdd(&a.log_rho[(int64_t)cell * K + i % K], v);
-            my_acc[i] = 0.0;
+        for (int j = lane; j < Tn; j += 32) {
+            const int cell = a.blk_cells[(int64_t)cur_cb * Tn + j];
+            for (int k = 0; k < K; ++k) {
+                const double v = my_acc[j * K + k];
+                if (cell >= 0 && v != 0.0) atomicAdd(&a.log_rho[(int64_t)cell * K + k], v);
+                my_acc[j * K + k] = 0.0;
+            }
         }
         __syncwarp();
     };
-    int64_t s = claim();
-    while (s < a.S) {
-        const int64_t s_following = claim();    // claimed early: its round trip hides behind this slice
-        const int cb = a.slice_cb[s];
+    int64_t run = claim();
+    while (run < a.S) {
+        const int64_t run_following = claim();  // claimed early: its round trip hides behind this run
+        const int64_t run_end = min(run + chunk, a.S);
+        // slice metadata is fetched one slice ahead, so that only the first slice of a run waits for it
+        int n_cb = a.slice_cb[run], n_m = a.slice_region[run], n_L = a.slice_len[run];
+        int64_t n_xb = a.slice_xbase[run], n_yb = a.slice_ybase[run];
+        int n_cell = a.lane_cell[run * 32 + lane], n_meta = a.lane_meta[run * 32 + lane];
+        for (int64_t s = run; s < run_end; ++s) {
+        const int cb = n_cb, m = n_m, L = n_L, cell = n_cell, meta = n_meta;
+        const int64_t xb = n_xb, yb = n_yb;
+        if (s + 1 < run_end) {
+            n_cb = a.slice_cb[s + 1]; n_m = a.slice_region[s + 1]; n_L = a.slice_len[s + 1];
+            n_xb = a.slice_xbase[s + 1]; n_yb = a.slice_ybase[s + 1];
+            n_cell = a.lane_cell[(s + 1) * 32 + lane]; n_meta = a.lane_meta[(s + 1) * 32 + lane];
+        }
         if (cb != cur_cb) {
             flush();
             cur_cb = cb;
         }
-        const int m = a.slice_region[s];
-        const int L = a.slice_len[s];
-        const int64_t xb = a.slice_xbase[s], yb = a.slice_ybase[s];
-        const int cell = a.lane_cell[s * 32 + lane];
-        const int meta = a.lane_meta[s * 32 + lane];
         const int len = meta & 0xffff, nl = meta >> 16;
         const bool valid = cell >= 0;
         const double *xrow = a.x_sell + xb + lane;
@@ -409,20 +422,27 @@ __global__ void __launch_bounds__(256, SWEEP_MINB) sweep_v2_kernel(SweepV2Args a
 #pragma unroll
         for (int u = 0; u < XU; ++u) xa[u] = xrow[u * 32];
         uint32_t yw = a.ybits[yb + lane];
+        constexpr int RK = 8;                   // responsibilities of the lane's cell, fetched up front when K <= 8
+        double rkv[RK];
+#pragma unroll
+        for (int k = 0; k < RK; ++k)
+            rkv[k] = UNIFORM_R ? inv_K : ((valid && k < K && K <= RK) ? a.r[(int64_t)cell * K + k] : 0.0);
         double *rec = a.stats + s * (R * 32) + (lane >> 2) * (R * 4) + (lane & 3);
         double hh[T];
 #pragma unroll
         for (int q = 0; q < T; ++q) hh[q] = rec[(D + q) * 4];
-        __syncwarp();
-        for (int i = lane; i < K * R; i += 32) my_u[i] = a.U[(int64_t)m * K * R + i];
-        __syncwarp();
+        if (m != cur_m) {                       // consecutive slices of a run mostly share the region
+            __syncwarp();
+            for (int i = lane; i < K * R; i += 32) my_u[i] = a.U[(int64_t)m * K * R + i];
+            __syncwarp();
+            cur_m = m;
+        }
         // -1/2 tr(H^T H (m m^T + S)) needs no E[z]: do it while the first CpG rows are in flight
         double wbar[D];
 #pragma unroll
         for (int d = 0; d < D; ++d) wbar[d] = 0.0;
-        for (int k = 0; k < K; ++k) {
+        auto pre_k = [&](int k, double rk) {
             const double *u = my_u + k * R;
-            const double rk = UNIFORM_R ? inv_K : (valid ? a.r[(int64_t)cell * K + k] : 0.0);
             double trc = 0.0;
 #pragma unroll
             for (int q = 0; q < T; ++q) trc = fma(u[D + q], hh[q], trc);
@@ -432,6 +452,13 @@ __global__ void __launch_bounds__(256, SWEEP_MINB) sweep_v2_kernel(SweepV2Args a
                 my_acc[nl * K + k] += trc;                 // lanes of one slice are distinct cells
                 if (WITH_LB) lb_local = fma(rk, trc, lb_local);
             }
+        };
+        if (K <= RK) {
+#pragma unroll
+            for (int k = 0; k < RK; ++k)
+                if (k < K) pre_k(k, rkv[k]);
+        } else {
+            for (int k = 0; k < K; ++k) pre_k(k, UNIFORM_R ? inv_K : (valid ? a.r[(int64_t)cell * K + k] : 0.0));
         }
         double g[D];
 #pragma unroll
@@ -507,7 +534,8 @@ __global__ void __launch_bounds__(256, SWEEP_MINB) sweep_v2_kernel(SweepV2Args a
                 my_acc[nl * K + k] += lin;
             }
         }
-        s = s_following;
+        }
+        run = run_following;
     }
     flush();
     if (WITH_LB) {
