@@ -249,6 +249,8 @@ def main():
         tp = os.path.join(ROOT, "profiles", "sweep_traffic.json")
         if os.path.exists(tp):
             traffic = json.load(open(tp)).get(args.workload)
+            if traffic is not None:
+                traffic = traffic / world          # captured on one GPU holding the whole job; a shard moves 1/world of it
         line["roofline"] = dict(bound="hbm", kernel="sweep_kernel", achieved=achieved, peak=peak, unit="GB/s",
                                 frac=achieved / peak, traffic=traffic, peak_source=peak_src,
                                 algorithmic_bytes_per_launch=alg_bytes, kernel_ms=sweep_ms,

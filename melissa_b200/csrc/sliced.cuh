@@ -626,8 +626,17 @@ __device__ __forceinline__ void dmma_m8n8k4(double &c0, double &c1, double a, do
                  : "d"(a), "d"(b));
 }
 
+#ifndef CMMA_UNROLL
+#define CMMA_UNROLL 8
+#endif
+#ifndef CMMA_MINB
+#define CMMA_MINB 4
+#endif
+#define CMMA_STR2(x) #x
+#define CMMA_STR(x) CMMA_STR2(x)
+#define CMMA_PRAGMA_UNROLL(n) _Pragma(CMMA_STR(unroll n))
 template <int MT, int NT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, CMMA_MINB)
 contract_mma_kernel(const int64_t *__restrict__ reg_slice_ptr, const int32_t *__restrict__ reg_slice,
                     const int32_t *__restrict__ lane_cell, const double *__restrict__ stats,
                     const double *__restrict__ r, double *__restrict__ acc_out, int K, int R) {
@@ -650,7 +659,7 @@ contract_mma_kernel(const int64_t *__restrict__ reg_slice_ptr, const int32_t *__
             const int64_t s = __shfl_sync(0xffffffffu, my_s, it);
             const int my_cell = lane_cell[s * 32 + lane];
             const double *rec = stats + s * ((int64_t)R * 32);
-#pragma unroll
+CMMA_PRAGMA_UNROLL(CMMA_UNROLL)
             for (int ks = 0; ks < 8; ++ks) {
                 const int pair = 4 * ks + tid4;
                 const int cell = __shfl_sync(0xffffffffu, my_cell, pair);
