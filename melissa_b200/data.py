@@ -38,6 +38,21 @@ class MelissaData:
         return dict(N=self.N, M=self.M, pair_ptr=self.pair_ptr, pair_cell=self.pair_cell,
                     pair_region=self.pair_region, x=self.x, y=self.y)
 
+    def save(self, path: str):
+        """Flat on-disk form (a compressed .npz of the five arrays + N, M): the format that lets a
+        real data set reach the GPU path without ever becoming a nested R list."""
+        np.savez_compressed(path, N=self.N, M=self.M, pair_ptr=self.pair_ptr, pair_cell=self.pair_cell,
+                            pair_region=self.pair_region, x=self.x, y=self.y,
+                            cell_names=np.asarray([] if self.cell_names is None else list(self.cell_names)))
+
+    @staticmethod
+    def load(path: str) -> "MelissaData":
+        z = np.load(path, allow_pickle=False)
+        names = [str(v) for v in z["cell_names"]] if "cell_names" in z.files and z["cell_names"].size else None
+        return MelissaData(N=int(z["N"]), M=int(z["M"]), pair_ptr=z["pair_ptr"].astype(np.int64),
+                           pair_cell=z["pair_cell"].astype(np.int32), pair_region=z["pair_region"].astype(np.int32),
+                           x=z["x"].astype(np.float64), y=z["y"].astype(np.uint8), cell_names=names)
+
     def shard_cells(self, lo: int, hi: int) -> "MelissaData":
         """Cells [lo, hi) as a stand-alone data set (cell indices re-based to 0)."""
         sel = np.flatnonzero((self.pair_cell >= lo) & (self.pair_cell < hi))

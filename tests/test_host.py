@@ -34,6 +34,15 @@ def test_nested_roundtrip_and_checks(c1):
         mdata.from_nested(X)                         # R/utils.R:69-71
 
 
+def test_flat_file_roundtrip(tmp_path, c1):
+    d = mdata.from_dict(c1)
+    d.cell_names = [f"cell_{i + 1}" for i in range(d.N)]
+    d.save(tmp_path / "synth.npz")
+    e = mdata.MelissaData.load(tmp_path / "synth.npz")
+    assert (e.N, e.M, e.P, e.nnz) == (d.N, d.M, d.P, d.nnz) and e.cell_names == d.cell_names
+    assert np.array_equal(e.x, d.x) and np.array_equal(e.y, d.y) and np.array_equal(e.pair_ptr, d.pair_ptr)
+
+
 def test_melissa_argument_checks(c1):
     d = mdata.from_dict(c1)
     with pytest.raises(ValueError):
