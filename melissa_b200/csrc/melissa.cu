@@ -1014,7 +1014,7 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
 size_t sweep_v2_smem(const melissa_handle *h, int nw) {
     const Sliced *sl = h->sl;
     return (size_t)sl->rt.n_entries * sizeof(double2) +
-           ((size_t)MILLS_N + 1 + (size_t)sl->Tn * h->K * nw + (size_t)nw * h->K * h->R) * sizeof(double);
+           ((size_t)MILLS_N + 1 + (size_t)sl->Tn * h->K * nw + (SWEEP_STAGE_U ? (size_t)nw * h->K * h->R : 0)) * sizeof(double);
 }
 
 int sweep_v2_warps(const melissa_handle *h) {

@@ -29,6 +29,9 @@ constexpr int MILLS_N = 2 * MILLS_HALF + 1;
 #ifndef SWEEP_MINB
 #define SWEEP_MINB 3
 #endif
+#ifndef SWEEP_STAGE_U
+#define SWEEP_STAGE_U 1     // 1: copy U[m] to shared memory per slice; 0: read it through L1 (uniform loads)
+#endif
 constexpr int RBF_SUB = 128;                  // table points per centre spacing
 constexpr double MAGIC = 6755399441055744.0;  // 1.5 * 2^52: (v + MAGIC) - MAGIC rounds v to an integer
 
@@ -363,7 +366,7 @@ __global__ void __launch_bounds__(256, SWEEP_MINB) sweep_v2_kernel(SweepV2Args a
     double2 *s_rbf = reinterpret_cast<double2 *>(smem_raw);
     double *s_mills = reinterpret_cast<double *>(s_rbf + a.rt.n_entries);
     double *s_u = s_mills + MILLS_N + 1;
-    double *s_acc = s_u + nw * K * R;
+    double *s_acc = s_u + (SWEEP_STAGE_U ? nw * K * R : 0);
     for (int i = threadIdx.x; i < a.rt.n_entries; i += blockDim.x) s_rbf[i] = a.rbf_tab[i];
     for (int i = threadIdx.x; i < MILLS_N; i += blockDim.x) s_mills[i] = a.mills_tab[i];
     for (int i = threadIdx.x; i < nw * Tn * K; i += blockDim.x) s_acc[i] = 0.0;
@@ -431,7 +434,8 @@ __global__ void __launch_bounds__(256, SWEEP_MINB) sweep_v2_kernel(SweepV2Args a
         double hh[T];
 #pragma unroll
         for (int q = 0; q < T; ++q) hh[q] = rec[(D + q) * 4];
-        if (m != cur_m) {                       // consecutive slices of a run mostly share the region
+        const double *um = SWEEP_STAGE_U ? my_u : a.U + (int64_t)m * K * R;
+        if (SWEEP_STAGE_U && m != cur_m) {      // consecutive slices of a run mostly share the region
             __syncwarp();
             for (int i = lane; i < K * R; i += 32) my_u[i] = a.U[(int64_t)m * K * R + i];
             __syncwarp();
@@ -442,7 +446,7 @@ __global__ void __launch_bounds__(256, SWEEP_MINB) sweep_v2_kernel(SweepV2Args a
 #pragma unroll
         for (int d = 0; d < D; ++d) wbar[d] = 0.0;
         auto pre_k = [&](int k, double rk) {
-            const double *u = my_u + k * R;
+            const double *u = um + k * R;
             double trc = 0.0;
 #pragma unroll
             for (int q = 0; q < T; ++q) trc = fma(u[D + q], hh[q], trc);
@@ -527,7 +531,7 @@ __global__ void __launch_bounds__(256, SWEEP_MINB) sweep_v2_kernel(SweepV2Args a
         for (int d = 0; d < D; ++d) rec[d * 4] = g[d];
         if (valid) {
             for (int k = 0; k < K; ++k) {
-                const double *u = my_u + k * R;
+                const double *u = um + k * R;
                 double lin = 0.0;
 #pragma unroll
                 for (int d = 0; d < D; ++d) lin = fma(u[d], g[d], lin);
