@@ -215,3 +215,53 @@ def test_rare_path_positions_outside_the_table_and_far_tails():
     assert np.isfinite(g).all()
     np.testing.assert_allclose(res["lb"][1:], ref["lb"][1:], rtol=1e-8)
     np.testing.assert_allclose(res["r_nk"], ref["r_nk"], atol=1e-7)
+
+
+def test_full_size_c3_properties_and_shard_invariance(layout):
+    """BASELINE configs[2] at full size (5,000 x 1,000, K = 4, 1.25e8 CpGs, drawn on the device):
+    properties that need no oracle, and the same fit from two cell shards."""
+    if layout != "sliced-block128":
+        pytest.skip("one layout is enough at this size")
+    import torch
+    mb.set_option("cell_block", 0)
+    K, N, M = 4, 5000, 1000
+    data, tr = synth.generate_device(N, M, K, n_basis=4, seed=1, chunk_cells=25)
+    delta_0 = np.full(K, 0.51)
+    with mb.Engine(data, tr["basis"], K_hint=K) as eng:
+        res = eng.run(K, tr["w0"], delta_0, vb_max_iter=30)
+    lb = res["lb"][1:]
+    assert len(lb) == 3 and np.all(np.diff(lb) > 0)                          # ELBO increases
+    np.testing.assert_allclose(res["r_nk"].sum(axis=1), 1.0, atol=1e-12)
+    np.testing.assert_allclose((res["delta"] - delta_0).sum(), N, rtol=1e-12)
+    assert np.linalg.eigvalsh(res["W_Sigma"]).min() > 0
+    assert mb.cluster_ari(tr["C_true"], res["r_nk"]) == 1.0
+    # two shards of 2,500 cells, reduction buffers summed by hand
+    shards = []
+    for lo, hi in ((0, 2500), (2500, 5000)):
+        d, _ = synth.generate_device(N, M, K, n_basis=4, seed=1, cell_lo=lo, cell_hi=hi, N_total=N, chunk_cells=25)
+        shards.append(mb.Engine(d, tr["basis"], allow_empty_regions=True, K_hint=K))
+        del d
+    del data
+    torch.cuda.empty_cache()
+
+    class Pair:
+        def phase_a(self):
+            for e in shards: e.phase_a()
+            t = [e.reduce_tensor() for e in shards]
+            s = t[0] + t[1]
+            for x in t: x.copy_(s)
+        def phase_b(self, with_lb):
+            for e in shards: e.phase_b(with_lb)
+            if with_lb:
+                t = [e.lb_tensor() for e in shards]
+                s = t[0] + t[1]
+                for x in t: x.copy_(s)
+        def lower_bound(self):
+            return [e.lower_bound() for e in shards][0]
+    for e in shards:
+        e.begin(K, tr["w0"], delta_0, n_cells_total=N)
+    lb2, _, _ = mb.vb_loop(Pair(), 30, 1e-5)
+    r2 = np.concatenate([e.fetch()["r_nk"] for e in shards])
+    for e in shards: e.close()
+    np.testing.assert_allclose(lb2[1:], lb, rtol=1e-12)                      # <= 1e-12 drift across shard counts
+    assert np.array_equal(r2.argmax(1), res["r_nk"].argmax(1))
