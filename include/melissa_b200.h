@@ -171,6 +171,17 @@ int melissa_vb_fetch(melissa_handle *h, double *W, double *W_Sigma, double *r_nk
 /* Per-pair H^T E[z] of the last sweep, [P * D] row-major per pair (diagnostic / parity tests). */
 int melissa_vb_fetch_HtEz(melissa_handle *h, double *out);
 
+/*
+ * Per-pair penalised probit MLE on the packed data: the role of
+ * BPRMeth::infer_profiles_mle(model = "bernoulli", lambda = .5, opt_itnmax = 15) in the
+ * reference's default initialisation (call site R/melissa_vb.R:136-145).  Newton
+ * iterations on  sum_i log Phi(s_i h_i . w) - lambda |w|^2  for every covered pair.
+ * w_out[P * D] is a HOST buffer, pair-major in the order the pairs were passed to
+ * melissa_pack.  Needs the sliced layout.  (BPRMeth's optimiser is not in the reference
+ * tree; parity with it is statistical)
+ */
+int melissa_profiles_mle(melissa_handle *h, double lambda, int32_t n_iter, double *w_out);
+
 /* Block until all work queued on the handle's stream is done. */
 int melissa_sync(melissa_handle *h);
 

@@ -37,6 +37,7 @@ SIGNATURES = {
     "melissa_vb_lb_buffer": (C.c_int, [handle_t, C.POINTER(C.c_void_p), p_i64]),
     "melissa_vb_fetch": (C.c_int, [handle_t, p_dbl, p_dbl, p_dbl, p_dbl, p_dbl, p_dbl, p_dbl]),
     "melissa_vb_fetch_HtEz": (C.c_int, [handle_t, p_dbl]),
+    "melissa_profiles_mle": (C.c_int, [handle_t, c_dbl, c_i32, p_dbl]),
     "melissa_sync": (C.c_int, [handle_t]),
     "melissa_launch_count": (c_i64, [handle_t]),
     "melissa_impute": (C.c_int, [c_i32, c_i32, c_i32, c_i32, c_i32, p_dbl, c_dbl, p_dbl, p_dbl, c_i64, p_i64, p_i32,

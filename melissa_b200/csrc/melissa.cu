@@ -1334,6 +1334,45 @@ int melissa_pack_device(int32_t n_cells, int32_t n_regions, int64_t n_pairs, con
                      gamma, device, allow_empty_regions, true, out);
 }
 
+int melissa_profiles_mle(melissa_handle *h, double lambda, int32_t n_iter, double *w_out) {
+    if (!h) return fail(MELISSA_ERR_ARG, "handle is NULL");
+    if (!w_out) return fail(MELISSA_ERR_ARG, "w_out is NULL");
+    if (!(lambda >= 0.0) || n_iter < 1) return fail(MELISSA_ERR_ARG, "lambda >= 0 and n_iter >= 1 are required");
+    if (!h->sl) return fail(MELISSA_ERR_STATE, "melissa_profiles_mle needs the sliced layout (equally spaced RBF centres)");
+    CU(cudaSetDevice(h->device));
+    Sliced *sl = h->sl;
+    const int D = h->D;
+    double *d_out = nullptr;
+    int rc = dev_alloc(&d_out, sl->S * 32 * D);
+    if (rc) return rc;
+    const size_t smem = (size_t)sl->rt.n_entries * sizeof(double2) + ((size_t)MILLS_N + 1) * sizeof(double);
+    const int grid = (int)std::min<int64_t>((sl->S + 7) / 8, (int64_t)h->sm_count * 4);
+    auto run = [&]() -> int {
+        DISPATCH_D(D, {
+            auto kfn = mle_kernel<DD>;
+            CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            kfn<<<grid, 256, smem, h->stream>>>(sl->x_sell, sl->ybits, sl->slice_xbase, sl->slice_ybase, sl->slice_len,
+                                                sl->lane_meta, sl->mills_tab, sl->rbf_tab, sl->rt, h->basis, d_out, sl->S,
+                                                lambda, n_iter);
+        });
+        return MELISSA_OK;
+    };
+    if ((rc = run())) { cudaFree(d_out); return rc; }
+    h->launches++;
+    std::vector<double> buf((size_t)sl->S * 32 * D);
+    const cudaError_t e = cudaMemcpy(buf.data(), d_out, buf.size() * sizeof(double), cudaMemcpyDeviceToHost);
+    cudaFree(d_out);
+    if (e != cudaSuccess) return fail(MELISSA_ERR_CUDA, "melissa_profiles_mle failed: %s", cudaGetErrorString(e));
+    int64_t q = 0;
+    for (const auto &piece : sl->lane_pair)
+        for (size_t i = 0; i < piece.size(); ++i, ++q) {
+            const int32_t p = piece[i];
+            if (p < 0) continue;
+            for (int d = 0; d < D; ++d) w_out[(size_t)p * D + d] = buf[(size_t)q * D + d];
+        }
+    return MELISSA_OK;
+}
+
 int melissa_set_option(const char *key, int64_t value) {
     if (!key) return fail(MELISSA_ERR_ARG, "key is NULL");
     if (!std::strcmp(key, "cell_block")) {

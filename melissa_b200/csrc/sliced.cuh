@@ -703,3 +703,121 @@ CMMA_PRAGMA_UNROLL(CMMA_UNROLL)
         if (cl < K && j < R) acc_out[((int64_t)m * K + cl) * R + j] = v;
     }
 }
+
+// ---------------------------------------------------------------------------
+// Per-pair penalised probit MLE (the role of BPRMeth::infer_profiles_mle(model = "bernoulli",
+// lambda, opt_itnmax) in the default initialisation, reference R/melissa_vb.R:136-145): Newton
+// iterations on  sum_i log Phi(s_i h_i.w) - lambda |w|^2  for every covered (cell, region) pair.
+// One warp per slice, one lane per pair; gradient and Hessian are accumulated over the pair's
+// CpGs with the same table-driven basis / Mills-ratio code as the sweep, then a D x D Cholesky
+// solve per lane.  out[(slice * 32 + lane) * D + d]; padding lanes write zeros.
+// ---------------------------------------------------------------------------
+template <int D>
+__global__ void __launch_bounds__(256)
+mle_kernel(const double *__restrict__ x_sell, const uint32_t *__restrict__ ybits,
+           const int64_t *__restrict__ slice_xbase, const int64_t *__restrict__ slice_ybase,
+           const int32_t *__restrict__ slice_len, const int32_t *__restrict__ lane_meta,
+           const double *__restrict__ mills_tab, const double2 *__restrict__ rbf_tab, RbfTab rt, BasisDev basis,
+           double *__restrict__ out, int64_t S, double lambda, int n_iter) {
+    constexpr int T = D * (D + 1) / 2;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double2 *s_rbf = reinterpret_cast<double2 *>(smem_raw);
+    double *s_mills = reinterpret_cast<double *>(s_rbf + rt.n_entries);
+    for (int i = threadIdx.x; i < rt.n_entries; i += blockDim.x) s_rbf[i] = rbf_tab[i];
+    for (int i = threadIdx.x; i < MILLS_N; i += blockDim.x) s_mills[i] = mills_tab[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int64_t warp0 = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    for (int64_t s = warp0; s < S; s += nwarps) {
+        const int L = slice_len[s];
+        const int len = lane_meta[s * 32 + lane] & 0xffff;
+        const double *xrow = x_sell + slice_xbase[s] + lane;
+        const uint32_t *yrow = ybits + slice_ybase[s] + lane;
+        double w[D];
+#pragma unroll
+        for (int d = 0; d < D; ++d) w[d] = 0.0;
+        for (int it = 0; it < n_iter; ++it) {
+            double g[D], A[T];
+#pragma unroll
+            for (int d = 0; d < D; ++d) g[d] = 0.0;
+#pragma unroll
+            for (int q = 0; q < T; ++q) A[q] = 0.0;
+            uint32_t yw = 0;
+            for (int i = 0; i < L; ++i) {
+                if ((i & 31) == 0) yw = yrow[(int64_t)(i >> 5) * 32];
+                const bool yi = (yw >> (i & 31)) & 1u;
+                double h[D];
+                eval_basis_tab<D>(xrow[(int64_t)i * 32], rt, s_rbf, basis, h);
+                double eta = w[0];
+#pragma unroll
+                for (int d = 1; d < D; ++d) eta = fma(h[d], w[d], eta);
+                const double t = yi ? eta : -eta;
+                const double G = trunc_mean_tab(t, s_mills);     // t + phi/Phi
+                double lam = G - t;                              // phi(t) / Phi(t)
+                double hess = lam * G;                           // -(d^2/d eta^2) log Phi(s eta)
+                if (i >= len) { lam = 0.0; hess = 0.0; }
+                const double gr = yi ? lam : -lam;
+                int q = 0;
+#pragma unroll
+                for (int a2 = 0; a2 < D; ++a2) {
+                    g[a2] = fma(h[a2], gr, g[a2]);
+                    const double ha = h[a2] * hess;
+#pragma unroll
+                    for (int c2 = a2; c2 < D; ++c2) {
+                        A[q] = fma(ha, h[c2], A[q]);
+                        ++q;
+                    }
+                }
+            }
+            // Newton step: (A + 2 lambda I) step = g - 2 lambda w
+            double Lm[D][D];
+            {
+                int q = 0;
+#pragma unroll
+                for (int a2 = 0; a2 < D; ++a2) {
+                    g[a2] -= 2.0 * lambda * w[a2];
+#pragma unroll
+                    for (int c2 = a2; c2 < D; ++c2) {
+                        Lm[c2][a2] = A[q] + (a2 == c2 ? 2.0 * lambda : 0.0);
+                        ++q;
+                    }
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < D; ++j) {
+                double dd = Lm[j][j];
+#pragma unroll
+                for (int c2 = 0; c2 < j; ++c2) dd -= Lm[j][c2] * Lm[j][c2];
+                const double ljj = sqrt(dd), inv = 1.0 / ljj;
+                Lm[j][j] = ljj;
+#pragma unroll
+                for (int i2 = j + 1; i2 < D; ++i2) {
+                    double sacc = Lm[i2][j];
+#pragma unroll
+                    for (int c2 = 0; c2 < j; ++c2) sacc -= Lm[i2][c2] * Lm[j][c2];
+                    Lm[i2][j] = sacc * inv;
+                }
+            }
+            double z[D];
+#pragma unroll
+            for (int i2 = 0; i2 < D; ++i2) {                     // forward
+                double sacc = g[i2];
+#pragma unroll
+                for (int c2 = 0; c2 < i2; ++c2) sacc -= Lm[i2][c2] * z[c2];
+                z[i2] = sacc / Lm[i2][i2];
+            }
+#pragma unroll
+            for (int i2 = D - 1; i2 >= 0; --i2) {                // backward
+                double sacc = z[i2];
+#pragma unroll
+                for (int c2 = i2 + 1; c2 < D; ++c2) sacc -= Lm[c2][i2] * z[c2];
+                z[i2] = sacc / Lm[i2][i2];
+            }
+#pragma unroll
+            for (int d = 0; d < D; ++d) w[d] += z[d];
+        }
+#pragma unroll
+        for (int d = 0; d < D; ++d) out[(s * 32 + lane) * D + d] = len > 0 ? w[d] : 0.0;
+    }
+}

@@ -160,6 +160,12 @@ class Engine:
         _lib.check(self.lib.melissa_vb_fetch_HtEz(self.h, _lib.ptr(out, _lib.c_dbl)))
         return out
 
+    def profiles_mle(self, lam: float = 0.5, n_iter: int = 15):
+        """Per-pair penalised probit MLE on the GPU, [P, D] (melissa_profiles_mle)."""
+        out = np.empty((self.P, self.D), np.float64)
+        _lib.check(self.lib.melissa_profiles_mle(self.h, float(lam), int(n_iter), _lib.ptr(out, _lib.c_dbl)))
+        return out
+
     def sync(self):
         _lib.check(self.lib.melissa_sync(self.h))
 

@@ -74,7 +74,12 @@ def initial_w(engine, data, basis, K, delta_0, alpha_0, beta_0, epsilon_conv, is
     whose mini-VB ends with the best lower bound contributes its INITIAL w
     (:187-193), and vb_init_nstart == 1 skips the mini-VB (:174-177)."""
     N, M, D = data.N, data.M, int(basis["M"]) + 1
-    w_mle = probit_mle(data, basis)
+    try:
+        w_mle = engine.profiles_mle(0.5, 15)             # GPU (sliced layout)
+    except Exception as exc:                             # flat layout: the same Newton iterations in NumPy
+        if "sliced layout" not in str(exc):
+            raise
+        w_mle = probit_mle(data, basis)
     ww = rng.normal(0.0, 0.01, size=(M, D, N))                               # :148
     ww[data.pair_region, :, data.pair_cell] = w_mle                          # :151
     W_tmp = ww.transpose(2, 1, 0).reshape(N, D * M)                          # c(ww[,,n]) column-major
