@@ -267,6 +267,17 @@ def main():
         line["pairs"], line["cpgs"] = P_tot, nnz_tot
         line["setup_s"] = dict(generate=round(t_gen, 2), pack=round(t_pack, 2))
         line["check"] = dict(ari_vs_truth_rank0=ari, last_lb=[v for v in lbs if v is not None][-1:] or None)
+    # ---- time-to-converge under the reference's own stopping rule (|dLB| < 1e-5 tested every 10th iteration,
+    #      cap 300: R/melissa_vb.R:309, :458, :499), data resident; every rank runs the same loop
+    eng.begin(K, tr["w0"], delta_0, n_cells_total=wl["N"])
+    sync()
+    t0 = time.perf_counter()
+    lb_c, it_c, flags_c = mb.vb_loop(eng, 300, 1e-5, LB_EVERY, group=group)
+    sync()
+    t_conv = time.perf_counter() - t0
+    if rank == 0:
+        line["time_to_converge"] = dict(seconds=t_conv, iterations=int(it_c) - 1, flags=int(flags_c), lb=float(lb_c[-1]),
+                                        rule="abs(LB - LB_prev) < 1e-5 every 10th iteration, vb_max_iter = 300")
     # ---- end to end through the public API from HOST buffers (pack + H2D + K iterations + D2H of the result)
     e2e = None
     if not args.no_e2e:
@@ -317,6 +328,9 @@ def main():
             n_s = args.cpu_sample_cells or max(40, min(wl["N"], int(2.0e6 / wl["M"])))
             d, trs = synth.generate(n_s, wl["M"], K, n_basis=wl["n_basis"], seed=wl["seed"], N_total=n_s)
             r = cpu_port_run(d.as_dict(), K, trs["basis"], trs["w0"], 10, 0)
+            if "time_to_converge" in line:      # the same number of iterations on the host cores, from the sampled rate
+                line["time_to_converge"]["cpu_port_seconds_extrapolated"] = \
+                    P_tot * line["time_to_converge"]["iterations"] / r["value"]
             line["cpu_baseline"] = dict(value=r["value"], unit=UNIT, cores=r["cores"], kind="port",
                                         sample="%d cells x %d regions (%d pairs) of the same recipe, %d iterations, "
                                                "loop only" % (n_s, wl["M"], r["P"], r["iters"]))
