@@ -1,0 +1,63 @@
+/*
+ * .Call glue between R and libmelissa_b200.so.  Written without an R
+ * installation at hand: it has never been compiled.  It is the only file that includes R
+ * headers; the library itself is R-free.
+ *
+ *   R CMD SHLIB melissa_R.c -I../../include -L../../melissa_b200 -lmelissa_b200
+ */
+#include <R.h>
+#include <Rinternals.h>
+#include "melissa_b200.h"
+
+/* X: list (cells) of lists (regions) of I x 2 REALSXP or logical NA.  Walk it twice: count, then fill. */
+SEXP C_melissa_fit(SEXP X, SEXP K_, SEXP basis_M, SEXP mus, SEXP gamma, SEXP w0, SEXP delta_0,
+                   SEXP alpha_0, SEXP beta_0, SEXP max_iter, SEXP eps) {
+    const int N = LENGTH(X), M = LENGTH(VECTOR_ELT(X, 0)), K = asInteger(K_), nb = asInteger(basis_M), D = nb + 1;
+    R_xlen_t P = 0, nnz = 0;
+    for (int n = 0; n < N; ++n) for (int m = 0; m < M; ++m) {
+        SEXP r = VECTOR_ELT(VECTOR_ELT(X, n), m);
+        if (TYPEOF(r) == REALSXP && isMatrix(r)) { ++P; nnz += nrows(r); }
+    }
+    int64_t *ptr = (int64_t *) R_alloc(P + 1, sizeof(int64_t));
+    int32_t *cell = (int32_t *) R_alloc(P, sizeof(int32_t)), *reg = (int32_t *) R_alloc(P, sizeof(int32_t));
+    double *x = (double *) R_alloc(nnz, sizeof(double));
+    uint8_t *y = (uint8_t *) R_alloc(nnz, 1);
+    R_xlen_t p = 0, c = 0; ptr[0] = 0;
+    for (int n = 0; n < N; ++n) for (int m = 0; m < M; ++m) {
+        SEXP r = VECTOR_ELT(VECTOR_ELT(X, n), m);
+        if (!(TYPEOF(r) == REALSXP && isMatrix(r))) continue;
+        const int I = nrows(r); const double *v = REAL(r);          /* column-major: x = v[0..I), y = v[I..2I) */
+        for (int i = 0; i < I; ++i) { x[c] = v[i]; y[c] = (uint8_t) v[I + i]; ++c; }
+        cell[p] = n; reg[p] = m; ptr[++p] = c;
+    }
+    melissa_handle *h = NULL;
+    melissa_set_option("clusters_hint", K);                          /* lets the packer size its cell blocks for this K */
+    if (melissa_pack(N, M, P, ptr, cell, reg, x, y, MELISSA_BASIS_RBF, nb, REAL(mus), asReal(gamma), 0, 0, &h))
+        error("%s", melissa_last_error());                           /* e.g. "No coverage across all regions. ..." */
+    const int cap = asInteger(max_iter) / 10 + 3;
+    SEXP W = PROTECT(alloc3DArray(REALSXP, M, D, K)), S = PROTECT(allocVector(REALSXP, (R_xlen_t) K * M * D * D));
+    SEXP r_nk = PROTECT(allocMatrix(REALSXP, N, K)), delta = PROTECT(allocVector(REALSXP, K));
+    SEXP alpha = PROTECT(allocVector(REALSXP, K)), beta = PROTECT(allocVector(REALSXP, K));
+    SEXP pi_k = PROTECT(allocVector(REALSXP, K)), lb = PROTECT(allocVector(REALSXP, cap));
+    int n_lb = 0, n_iter = 0, flags = 0;
+    const double b0 = isNull(beta_0) ? R_NaN : asReal(beta_0);       /* NaN = default sqrt(alpha_k), :271-273 */
+    const int rc = melissa_vb_run(h, K, REAL(w0), REAL(delta_0), asReal(alpha_0), b0, asInteger(max_iter),
+                                  asReal(eps), 10, REAL(W), REAL(S), REAL(r_nk), REAL(delta), REAL(alpha),
+                                  REAL(beta), REAL(pi_k), REAL(lb), cap, &n_lb, &n_iter, &flags);
+    melissa_free(h);                                                 /* free BEFORE any R error / longjmp */
+    if (rc) error("%s", melissa_last_error());
+    SEXP out = PROTECT(allocVector(VECSXP, 10));
+    SET_VECTOR_ELT(out, 0, W); SET_VECTOR_ELT(out, 1, S); SET_VECTOR_ELT(out, 2, r_nk);
+    SET_VECTOR_ELT(out, 3, delta); SET_VECTOR_ELT(out, 4, alpha); SET_VECTOR_ELT(out, 5, beta);
+    SET_VECTOR_ELT(out, 6, pi_k); SET_VECTOR_ELT(out, 7, lengthgets(lb, n_lb));
+    SET_VECTOR_ELT(out, 8, ScalarInteger(n_iter)); SET_VECTOR_ELT(out, 9, ScalarInteger(flags));
+    UNPROTECT(9);
+    return out;
+}
+
+static const R_CallMethodDef call_methods[] = {{"C_melissa_fit", (DL_FUNC) &C_melissa_fit, 11}, {NULL, NULL, 0}};
+
+void R_init_melissaB200(DllInfo *dll) {
+    R_registerRoutines(dll, NULL, call_methods, NULL, NULL);
+    R_useDynamicSymbols(dll, FALSE);
+}
