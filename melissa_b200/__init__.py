@@ -6,6 +6,7 @@ Public surface mirrors the reference's R functions for this path:
 `eval_cluster_performance` (R/utils.R).  The arithmetic runs in
 libmelissa_b200.so (CUDA, sm_100a); there is no CPU fallback.
 """
+from . import _lib
 from .data import MelissaData, create_rbf_object, from_dict, from_nested, to_nested
 from .engine import Engine, set_option
 from .evaluate import (cluster_ari, eval_cluster_performance, eval_imputation_performance,

@@ -284,3 +284,24 @@ def test_profiles_mle_matches_the_numpy_newton_iterations(c1, layout):
     with mb.Engine(d2, tr["basis"]) as eng:
         got = eng.profiles_mle(0.5, 8)
     np.testing.assert_allclose(got, want, rtol=1e-8, atol=1e-9)
+
+
+def test_argument_errors_through_the_abi(c1):
+    d = mb.from_dict(c1)
+    with mb.Engine(d, c1["basis"]) as eng:
+        with pytest.raises(ValueError, match="shape"):
+            eng.run(2, c1["w0_k3"], c1["k2_delta_0"])                       # w has K = 3 clusters
+        with pytest.raises(mb._lib.MelissaError, match="K must be in 1..64"):
+            eng.run(65, np.zeros((d.M, 4, 65)), np.full(65, 0.5))
+        with pytest.raises(mb._lib.MelissaError, match="delta_0 must be positive"):
+            eng.run(2, c1["w0_k2"], np.array([0.5, -1.0]))
+        with pytest.raises(mb._lib.MelissaError, match="vb_max_iter"):
+            eng.run(2, c1["w0_k2"], c1["k2_delta_0"], vb_max_iter=1)
+        with pytest.raises(mb._lib.MelissaError, match="positive"):
+            eng.run(2, c1["w0_k2"], c1["k2_delta_0"], beta_0=-1.0)
+    bad = mb.from_dict(c1)
+    bad.y = bad.y.copy(); bad.y[5] = 2
+    with pytest.raises(mb._lib.MelissaError, match="not 0/1"):
+        mb.Engine(bad, c1["basis"])
+    with pytest.raises(mb._lib.MelissaError, match="0..7"):
+        mb.Engine(d, mb.create_rbf_object(9))
