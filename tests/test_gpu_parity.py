@@ -305,3 +305,30 @@ def test_argument_errors_through_the_abi(c1):
         mb.Engine(bad, c1["basis"])
     with pytest.raises(mb._lib.MelissaError, match="0..7"):
         mb.Engine(d, mb.create_rbf_object(9))
+
+
+@pytest.mark.parametrize("case", ["K1", "M1", "single_cpg_pairs", "two_iterations", "one_cell_per_region_block"])
+def test_edge_shapes_vs_oracle(case):
+    rng = np.random.RandomState(5)
+    K, n_basis, iters = 3, 3, 12
+    if case == "K1":
+        K = 1
+    d, tr = synth.generate(40, 1 if case == "M1" else 12, K, n_basis=n_basis, seed=17, sites_per_region=50,
+                           cov_lo=0.1, cov_hi=0.5)
+    if case == "single_cpg_pairs":                     # every pair keeps only its first CpG
+        first = d.pair_ptr[:-1]
+        d = mb.MelissaData(N=d.N, M=d.M, pair_ptr=np.arange(d.P + 1, dtype=np.int64), pair_cell=d.pair_cell,
+                           pair_region=d.pair_region, x=d.x[first].copy(), y=d.y[first].copy())
+    if case == "two_iterations":
+        iters = 2                                      # the loop runs i = 2 only; the bound is taken at vb_max_iter
+    if case == "one_cell_per_region_block":
+        mb.set_option("cell_block", 32)                # 40 cells -> a full block and a block of 8
+    w0 = tr["w0"] if case != "M1" else tr["w0"][:1]
+    delta_0 = np.full(K, 0.7)
+    ref = mo.melissa_inner(d.as_dict(), K, tr["basis"], w0, delta_0, vb_max_iter=iters)
+    with mb.Engine(d, tr["basis"], K_hint=K) as eng:
+        res = eng.run(K, w0, delta_0, vb_max_iter=iters)
+    assert len(res["lb"]) == len(ref["lb"]) and res["n_iter"] == ref["n_iter"] and res["flags"] == ref["flags"]
+    np.testing.assert_allclose(res["lb"][1:], ref["lb"][1:], rtol=LB_RTOL)
+    np.testing.assert_allclose(res["r_nk"], ref["r_nk"], atol=1e-8)
+    np.testing.assert_allclose(res["W"], ref["W"], atol=1e-7)
