@@ -108,6 +108,7 @@ struct melissa_handle {
     std::vector<cudaEvent_t> prof_ev;      // start/stop pairs
     std::vector<int> prof_id;
     Sliced *sl = nullptr;                  // v2 layout (sliced.cuh); null = v1 path
+    int sweep_grid[2][2] = {{0, 0}, {0, 0}};   // cached launch grid of the sweep variants (0 = not configured yet)
 };
 
 namespace {
@@ -1046,11 +1047,16 @@ int launch_sweep_v2(melissa_handle *h, bool with_lb, bool uniform_r) {
 #define SWEEP2(LB_, UNI_)                                                                                   \
     DISPATCH_D(h->D, {                                                                                      \
         auto kfn = sweep_v2_kernel<DD, LB_, UNI_>;                                                          \
-        CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));              \
-        CU(cudaFuncSetAttribute(kfn, cudaFuncAttributePreferredSharedMemoryCarveout, 100));                 \
-        int per_sm = 1;                                                                                     \
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, block, smem));                       \
-        grid = (int)std::min<int64_t>((sl->S + nw - 1) / nw, (int64_t)h->sm_count * std::max(1, per_sm));  \
+        int &cached = h->sweep_grid[LB_ ? 1 : 0][UNI_ ? 1 : 0];   /* attributes / occupancy: once per fit */ \
+        if (cached == 0) {                                                                                  \
+            /* the opt-in limit is per function, not per handle: ask for the most any fit can need */     \
+            CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));         \
+            CU(cudaFuncSetAttribute(kfn, cudaFuncAttributePreferredSharedMemoryCarveout, 100));             \
+            int per_sm = 1;                                                                                 \
+            CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, block, smem));                   \
+            cached = (int)std::min<int64_t>((sl->S + nw - 1) / nw, (int64_t)h->sm_count * std::max(1, per_sm)); \
+        }                                                                                                   \
+        grid = cached;                                                                                      \
         a.chunk = std::max<int64_t>(1, std::min<int64_t>(64, sl->S / ((int64_t)grid * nw * 4)));            \
         kfn<<<grid, block, smem, h->stream>>>(a);                                                           \
     })
@@ -1448,6 +1454,7 @@ int melissa_vb_begin(melissa_handle *h, int32_t K, const double *w0, const doubl
         if (!(delta_0[k] > 0.0)) return fail(MELISSA_ERR_ARG, "delta_0 must be positive");
     CU(cudaSetDevice(h->device));
     free_fit(h);
+    for (auto &row : h->sweep_grid) row[0] = row[1] = 0;
     h->K = K;
     h->stream = (cudaStream_t)stream;
     h->N_total = n_cells_total;
