@@ -12,7 +12,7 @@ mp.mp.dps = 40
 MAGIC = 6755399441055744.0
 
 
-def trunc_mean_table(t, sp=128, order=6):
+def trunc_mean_table(t, sp=128, order=5):
     """E[z | z > 0], z ~ N(t, 1): t + 1 / R(t), R = Phi / phi from a table at spacing 1/sp and the
     recurrence c_{n+1} = (c_{n-1} + t0 c_n) / (n + 1) (trunc_mean_tab in sliced.cuh)."""
     v = t * sp + MAGIC
