@@ -255,12 +255,12 @@ def main():
                                 frac=achieved / peak, traffic=traffic, peak_source=peak_src,
                                 algorithmic_bytes_per_launch=alg_bytes, kernel_ms=sweep_ms,
                                 whole_step_frac=(algorithmic_bytes(nnz_tot, P_tot, D) / world) / (ms / steps * 1e-3) / 1e9 / peak)
-        # second view of the same kernel: it is FP64-issue bound, not HBM bound.  71 FP64
-        # operations per CpG in the row loop (27 basis, 4 dot, 27 truncated-normal mean, 5 accumulate, 8 misc) plus
+        # second view of the same kernel: it is FP64-issue bound, not HBM bound.  70 FP64
+        # operations per CpG in the row loop (26 basis, 4 dot, 27 truncated-normal mean, 5 accumulate, 8 misc) plus
         # 25 K per pair; peak = DFMA rate measured on this pool's B200 with tools/fp64_peak.cu.
-        fp64_ops = 71.0 * nnz_loc + 25.0 * K * P_loc
+        fp64_ops = 70.0 * nnz_loc + 25.0 * K * P_loc
         line["fp64"] = dict(achieved=fp64_ops / (sweep_ms * 1e-3) / 1e12, peak=18.1, unit="T FP64 op/s",
-                            frac=fp64_ops / (sweep_ms * 1e-3) / 1e12 / 18.1, ops_per_cpg=71, ops_per_pair=25 * K)
+                            frac=fp64_ops / (sweep_ms * 1e-3) / 1e12 / 18.1, ops_per_cpg=70, ops_per_pair=25 * K)
         line["kernels_ms_per_step"] = {k: v[0] / steps for k, v in prof.items()}
         line["gpu_launches"] = launches
         line["clocks"] = clocks

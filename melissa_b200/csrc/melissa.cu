@@ -938,7 +938,7 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
         rbf_tab.resize((size_t)rt.n_entries);
         for (int k = k_lo; k <= k_hi; ++k) {
             const double u0 = (double)k * rt.s;
-            rbf_tab[(size_t)(k - k_lo)] = make_double2(std::exp(-b.gamma * u0 * u0), std::exp(rt.g2d * u0));
+            rbf_tab[(size_t)(k - k_lo)] = make_double2(std::exp(-b.gamma * u0 * u0), rt.q * std::exp(rt.g2d * u0));
         }
     } else {
         rt = RbfTab{};

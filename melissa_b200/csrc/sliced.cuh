@@ -51,7 +51,7 @@ struct Sliced {
     int32_t *reg_slice = nullptr;         // [S]
     double *stats = nullptr;              // [S][8][R][4]
     double *mills_tab = nullptr;          // [MILLS_N]
-    double2 *rbf_tab = nullptr;           // [rt.n_entries] (E(u0), B(u0))
+    double2 *rbf_tab = nullptr;           // [rt.n_entries] (E(u0), q B(u0))
     RbfTab rt{};
     unsigned long long *slice_counter = nullptr;   // slice dispenser of the persistent sweep
     std::vector<std::vector<int32_t>> lane_pair;   // host, per build piece: original pair of (slice, lane), -1 = padding
@@ -94,7 +94,7 @@ __device__ __forceinline__ double trunc_mean_tab(double t, const double *__restr
 }
 
 // RBF row from the position, equally spaced centres mu_j = mu_1 + (j-1) Delta:
-//   h_1 = exp(-gamma u^2),  h_{j+1} = h_j * b * q^(2j-1),  u = x - mu_1,
+//   h_1 = exp(-gamma u^2),  h_{j+1} = h_j * b * q^(2j-1),  u = x - mu_1,   (the table stores q b)
 //   b = exp(2 gamma Delta u), q = exp(-gamma Delta^2).
 // exp(-gamma u^2) and b come from a table at u0 = k s (s = Delta / RBF_SUB) times short
 // series in the remainder d = u - u0 (|arguments| < 0.05).
@@ -130,7 +130,7 @@ __device__ __forceinline__ void eval_basis_tab(double x, const RbfTab &rt, const
         e = fma(z, e, 0.5);
         e = fma(z, e, 1.0);
         e = fma(z, e, 1.0);
-        double bj = (eb.y * e) * rt.q;
+        double bj = eb.y * e;                          // the table's second entry carries the factor q
 #pragma unroll
         for (int j = 2; j < D; ++j) {
             h[j] = h[j - 1] * bj;
@@ -190,7 +190,7 @@ __device__ __forceinline__ bool eval_basis_fast(double x, const RbfTab &rt, cons
         e = fma(z, e, 0.5);
         e = fma(z, e, 1.0);
         e = fma(z, e, 1.0);
-        double bj = (eb.y * e) * rt.q;
+        double bj = eb.y * e;                          // the table's second entry carries the factor q
 #pragma unroll
         for (int j = 2; j < D; ++j) {
             h[j] = h[j - 1] * bj;

@@ -37,7 +37,8 @@ def rbf_row_table(x, M, sub=128):
     v = u * (1.0 / s) + MAGIC
     u0 = (v - MAGIC) * s
     d = u - u0
-    E, B = np.exp(-gamma * u0 * u0), np.exp(2 * gamma * delta * u0)  # the table entries
+    q = math.exp(-gamma * delta * delta)
+    E, B = np.exp(-gamma * u0 * u0), q * np.exp(2 * gamma * delta * u0)  # the table entries (q folded into B)
     w = (-gamma * d) * (2 * u0 + d)
     c = np.full_like(w, 1.0 / 5040)
     for k in (720, 120, 24, 6, 2, 1, 1):
@@ -46,9 +47,8 @@ def rbf_row_table(x, M, sub=128):
     e = np.full_like(z, 1.0 / 720)
     for k in (120, 24, 6, 2, 1, 1):
         e = e * z + 1.0 / k
-    q = math.exp(-gamma * delta * delta)
     h = [E * c]
-    bj = (B * e) * q
+    bj = B * e
     for _ in range(1, M):
         h.append(h[-1] * bj)
         bj = bj * (q * q)
