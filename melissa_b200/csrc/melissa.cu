@@ -6,6 +6,14 @@
 // per-CpG sweep, a per-cell soft-max, a region-major contraction and a batched
 // D x D solve, see DESIGN.md.
 //
+// Two data layouts live in this translation unit:
+//   * region-sliced ELL (sliced.cuh): the default whenever the RBF centres are equally
+//     spaced -- persistent sweep with table-driven basis / truncated-normal mean,
+//     FP64 tensor-core contraction;
+//   * flat cell-major CSR (the kernels below without a _v2 / _mma suffix): the first
+//     correct path, kept for hand-placed centres and as an independent cross-check in
+//     the parity tests.
+//
 // Per-pair record ("stats"), R = D + T doubles, T = D(D+1)/2:
 //     [ g = H^T E[z]  (D) | packed upper triangle of H^T H  (T) ]
 // Per-(region, cluster) record ("U"), same length:
