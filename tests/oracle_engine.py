@@ -11,8 +11,9 @@ import melissa_oracle as mo
 
 
 class OracleEngine:
-    """Same phases and the same reduction-buffer layout as the CUDA library:
-    red = [acc (M*K*R) | colsum (K) | sum r log r], lbbuf = [lb_pz_qz, count]."""
+    """Same phases as the CUDA library and the same kind of reduction buffers (its own layout:
+    red = [acc (M*K*(D + D*D), full H^T H instead of the packed triangle) | colsum (K) | sum r log r],
+    lbbuf = [lb_pz_qz, count]); what is shared with the product is vb.vb_loop, not the layout."""
 
     def __init__(self, data, basis):
         self.d, self.basis = data, basis
