@@ -104,8 +104,34 @@ def cluster_ari(C_true, r_nk) -> float:
     return adjusted_rand_index(first_max(C_true), first_max(r_nk))
 
 
+def _align_cluster(Z1, Z2):
+    """R/utils.R:646-719 (`.align_cluster`, type = "mat"): harden both assignment matrices, then greedily
+    swap pairs of columns of the estimate while that increases the number of matching entries.
+    (R's max.col breaks ties at random; the first maximum is taken here.)"""
+    Z1, Z2 = np.asarray(Z1, np.float64), np.asarray(Z2, np.float64)
+    N, K = Z1.shape
+    L1 = np.zeros((N, K)); Lm = np.zeros((N, K))
+    L1[np.arange(N), Z1.argmax(1)] = 1
+    Lm[np.arange(N), Z2.argmax(1)] = 1
+    for k in range(K):
+        for tempk in range(K):
+            best = np.sum(L1 == Lm)
+            dummy = Lm.copy()
+            dummy[:, k], dummy[:, tempk] = Lm[:, tempk], Lm[:, k]
+            if np.sum(L1 == dummy) > best:
+                Lm = dummy
+    return Lm
+
+
+def cluster_error(C_true, C_post) -> float:
+    """R/utils.R:597-607: share of assignment-matrix entries that differ after aligning the labels."""
+    C_true = np.asarray(C_true, np.float64)
+    aligned = _align_cluster(C_true, C_post)
+    return float(1.0 - np.sum(aligned == C_true) / C_true.size)
+
+
 def eval_cluster_performance(obj, C_true):
-    """R/utils.R:572-580 (ARI only; the label-alignment error needs .align_cluster)."""
+    """R/utils.R:572-580: obj["clustering"] = list(error, ari)."""
     obj = type(obj)(obj)
-    obj["clustering"] = dict(ari=cluster_ari(C_true, obj["r_nk"]))
+    obj["clustering"] = dict(error=cluster_error(C_true, obj["r_nk"]), ari=cluster_ari(C_true, obj["r_nk"]))
     return obj

@@ -111,6 +111,19 @@ def test_eval_metrics_match_oracle():
     assert evaluate.adjusted_rand_index(lab, (lab + 1) % 3) == 1.0
 
 
+def test_cluster_error_aligns_labels_first():
+    rng = np.random.RandomState(2)
+    lab = rng.randint(0, 3, 60)
+    C_true = np.eye(3)[lab]
+    post = np.eye(3)[(lab + 1) % 3] * 0.9 + 0.05                 # same clustering, labels rotated
+    assert evaluate.cluster_error(C_true, post) == 0.0           # R/utils.R:597-607 after .align_cluster
+    post2 = post.copy()
+    post2[:6] = post2[:6][:, [1, 2, 0]]                          # six cells moved to another cluster
+    assert abs(evaluate.cluster_error(C_true, post2) - 2 * 6 / C_true.size) < 1e-12
+    out = evaluate.eval_cluster_performance(vb.MelissaResult(r_nk=post), C_true)
+    assert out["clustering"]["ari"] == 1.0 and out["clustering"]["error"] == 0.0
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
