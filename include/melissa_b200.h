@@ -224,11 +224,10 @@ int melissa_impute(int32_t n_cells, int32_t n_regions, int32_t K, int32_t basis_
  *
  * Who needs it: a host process in which some other runtime has already claimed
  * all of the GPU's memory for its own pool, so that one more cudaMalloc fails; or
- * a service that imputes a small batch per request and may not enter the CUDA
- * allocator at that point (for instance because another thread of the process is
- * in the middle of a stream capture).  melissa_impute allocates and frees seven
- * device buffers on every call; this variant calls no cudaMalloc / cudaFree and
- * no allocating library routine.  Instead it stages its inputs and its output in
+ * a service that imputes a small batch per request and wants neither the CUDA
+ * allocator nor cudaFree's device-wide synchronisation in its request path.
+ * melissa_impute allocates and frees seven device buffers on every call; this
+ * variant calls no cudaMalloc / cudaFree and no allocating library routine.  Instead it stages its inputs and its output in
  * a fixed array of MELISSA_NOALLOC_SCRATCH_BYTES that is part of the library
  * image -- every GPU that loads the library holds that much memory until the
  * process exits, whether or not this function is ever called.
@@ -241,7 +240,10 @@ int melissa_impute(int32_t n_cells, int32_t n_regions, int32_t K, int32_t basis_
  *     use melissa_impute;
  *   - the first call on a device looks up the array's device address
  *     (cudaGetSymbolAddress, once per device).  Make that first call before any
- *     stream capture starts;
+ *     stream capture starts.  The call copies and launches on the default stream
+ *     and blocks the calling thread until the result is back;
+ *   - pair_ptr[0] must be 0 (as for melissa_impute); the caller's current device is
+ *     left as it was;
  *   - all calls share the one array and it keeps the previous call's bytes.  The
  *     function overwrites everything it reads before it launches, so stale
  *     contents are harmless, but two calls that are in flight at the same time on

@@ -1,6 +1,7 @@
 """Build the CUDA shared library in-tree (nvcc, sm_100a only)."""
 from __future__ import annotations
 
+import glob
 import os
 import shutil
 import subprocess
@@ -9,7 +10,8 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(PKG_DIR)
 LIB_PATH = os.path.join(PKG_DIR, "libmelissa_b200.so")
 SOURCES = [os.path.join(PKG_DIR, "csrc", "melissa.cu")]
-HEADERS = [os.path.join(PKG_DIR, "csrc", "special.cuh"), os.path.join(ROOT, "include", "melissa_b200.h")]
+HEADERS = sorted(glob.glob(os.path.join(PKG_DIR, "csrc", "*.cuh")) + glob.glob(os.path.join(PKG_DIR, "csrc", "*.h")) +
+                 glob.glob(os.path.join(ROOT, "include", "*.h")))
 
 
 def nvcc_path() -> str:

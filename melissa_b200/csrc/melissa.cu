@@ -1721,6 +1721,7 @@ int melissa_impute(int32_t n_cells, int32_t n_regions, int32_t K, int32_t basis_
             return fail(MELISSA_ERR_ARG, "test pair %lld: cell/region index out of range", (long long)p);
         if (pair_ptr[p + 1] < pair_ptr[p]) return fail(MELISSA_ERR_ARG, "test pair_ptr must be non-decreasing");
     }
+    if (pair_ptr[0] != 0) return fail(MELISSA_ERR_ARG, "test pair_ptr[0] must be 0");
     CU(cudaSetDevice(device));
     BasisDev basis{};
     const int D = n_basis + 1;
@@ -1770,11 +1771,12 @@ int melissa_impute(int32_t n_cells, int32_t n_regions, int32_t K, int32_t basis_
 // cudaMalloc's and frees on every call.  A host that must not (or cannot)
 // allocate device memory -- a process whose GPU memory has been handed in full
 // to another runtime's pool, so that a further cudaMalloc fails; a service that
-// imputes one small batch per request and may not touch the allocator while some
-// other thread of the process has a stream capture open -- gets the same result
-// from the entry point below: the staging area is this fixed array, which lives
-// in the library image (every GPU that loads the library holds these bytes until
-// the process exits).
+// imputes one small batch per request and has to keep the allocator (and the
+// implicit synchronisation of cudaFree) out of its request path -- gets the same
+// result from the entry point below: the staging area is this fixed array, which
+// lives in the library image (every GPU that loads the library holds these bytes
+// until the process exits).  The copies and the launch go through the default
+// stream and block the calling thread.
 //
 // `g_noalloc_scratch` is only a host-side handle here; the kernel needs the
 // device address, obtained once per device with cudaGetSymbolAddress while that
@@ -1816,6 +1818,7 @@ int melissa_impute_noalloc(int32_t n_cells, int32_t n_regions, int32_t K, int32_
             return fail(MELISSA_ERR_ARG, "test pair %lld: cell/region index out of range", (long long)p);
         if (pair_ptr[p + 1] < pair_ptr[p]) return fail(MELISSA_ERR_ARG, "test pair_ptr must be non-decreasing");
     }
+    if (pair_ptr[0] != 0) return fail(MELISSA_ERR_ARG, "test pair_ptr[0] must be 0");
     const int D = n_basis + 1;
     const int64_t nnz = pair_ptr[n_pairs];
     // carve the fixed array: every piece starts on a 256-byte boundary
@@ -1830,6 +1833,12 @@ int melissa_impute_noalloc(int32_t n_cells, int32_t n_regions, int32_t K, int32_
                     "melissa_impute_noalloc: this call needs %lld bytes of device staging but the fixed scratch "
                     "array holds %lld; split the batch or use melissa_impute",
                     (long long)need, (long long)MELISSA_NOALLOC_SCRATCH_BYTES);
+    // the caller's current device is put back on every way out
+    struct DeviceGuard {
+        int prev = -1;
+        DeviceGuard() { if (cudaGetDevice(&prev) != cudaSuccess) prev = -1; }
+        ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+    } guard;
     unsigned char *base = nullptr;
     int rc = noalloc_device_ptr(device, &base);
     if (rc) return rc;
@@ -1843,8 +1852,9 @@ int melissa_impute_noalloc(int32_t n_cells, int32_t n_regions, int32_t K, int32_
     double *d_W = reinterpret_cast<double *>(cur); cur += sz_W;
     double *d_r = reinterpret_cast<double *>(cur);
     // The array keeps whatever the previous call left in it.  Nothing here relies on
-    // zeros: each input piece is overwritten in full before the launch, and the
-    // kernel writes every pred[i], i < nnz, before it is copied out.
+    // zeros: each input piece is overwritten in full before the launch, and because
+    // pair_ptr starts at 0 and is non-decreasing (checked above) the pairs tile
+    // [0, nnz), so the kernel writes every pred[i] before it is copied out.
     CU(cudaMemcpy(d_ptr, pair_ptr, (size_t)(n_pairs + 1) * sizeof(int64_t), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(d_cell, pair_cell, (size_t)n_pairs * sizeof(int32_t), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(d_reg, pair_region, (size_t)n_pairs * sizeof(int32_t), cudaMemcpyHostToDevice));

@@ -52,6 +52,45 @@ def test_noalloc_imputation_matches_the_allocating_entry_point_twice(c1):
         assert got.min() >= 0.0 and got.max() <= 1.0
 
 
+def test_noalloc_leaves_free_device_memory_and_the_current_device_alone(c1):
+    """The point of the entry point: between its first call on the device (which has
+    already happened or happens in the warm-up below) and any later call, the amount of
+    free device memory does not move and the caller's current device stays put."""
+    import torch
+    lib = _lib.load()
+    W, r = c1["k2_W"], c1["k2_r_nk"]
+    test = subset(c1, np.arange(c1["x"].shape[0]) % 3 == 0)
+    rc, _ = _call(lib.melissa_impute_noalloc, c1, W, r, test)          # warm-up: context, module load, address look-up
+    assert rc == 0, lib.melissa_last_error()
+    torch.cuda.synchronize()
+    dev_before = torch.cuda.current_device()
+    free_before, _tot = torch.cuda.mem_get_info(0)
+    for _ in range(3):
+        rc, got = _call(lib.melissa_impute_noalloc, c1, W, r, test)
+        assert rc == 0, lib.melissa_last_error()
+    free_after, _tot = torch.cuda.mem_get_info(0)
+    assert free_after == free_before
+    assert torch.cuda.current_device() == dev_before
+
+
+@pytest.mark.parametrize("entry", ["melissa_impute", "melissa_impute_noalloc"])
+def test_impute_rejects_a_pair_list_that_does_not_start_at_zero(c1, entry):
+    """pair_ptr[0] = c > 0 would leave pred[0..c) unwritten -- in the no-alloc variant that
+    means handing the PREVIOUS caller's bytes back; a negative value would read before x."""
+    lib = _lib.load()
+    W, r = c1["k2_W"], c1["k2_r_nk"]
+    test = subset(c1, np.ones(c1["x"].shape[0], bool))
+    rc, first = _call(getattr(lib, entry), c1, W, r, test)              # leaves its pred in the shared array
+    assert rc == 0
+    for shift in (3, -3):
+        bad = dict(test)
+        bad["pair_ptr"] = test["pair_ptr"].copy()
+        bad["pair_ptr"][0] = shift
+        rc, got = _call(getattr(lib, entry), c1, W, r, bad)
+        assert rc == 1 and "pair_ptr[0]" in lib.melissa_last_error().decode()
+        assert np.isnan(got).all()                                      # nothing was written to the caller's buffer
+
+
 def test_noalloc_refuses_a_batch_larger_than_its_fixed_array(c2):
     lib = _lib.load()
     cap = 8 << 20
