@@ -205,6 +205,14 @@ int melissa_profile_read(melissa_handle *h, int32_t kernel_id, double *total_ms,
 int64_t melissa_launch_count(const melissa_handle *h);
 
 /*
+ * Shape of the packed layout (diagnostic; bench.py reports the row padding from it).  No
+ * counterpart in the reference.  Writes up to 8 values: [0] 1 = region-sliced layout, 0 = flat;
+ * [1] cells per block; [2] slices; [3] stored CpG slots (rows x 32 lanes, padding included);
+ * [4] CpGs; [5] pairs; [6] chunks of the sweep; [7] warps per sweep CTA of the current fit.
+ */
+int melissa_layout_info(const melissa_handle *h, int64_t *out, int32_t n);
+
+/*
  * Imputation pass (reference impute_test_met with basis = NULL, is_predictive =
  * TRUE: R/utils.R:225-284): pred[i] = round(sum_k r_nk[n,k] * Phi(h(x_i) . W[m,,k]), 3)
  * for held-out CpGs given as the same kind of cell-major pair list (cells

@@ -40,6 +40,7 @@ SIGNATURES = {
     "melissa_profiles_mle": (C.c_int, [handle_t, c_dbl, c_i32, p_dbl]),
     "melissa_sync": (C.c_int, [handle_t]),
     "melissa_launch_count": (c_i64, [handle_t]),
+    "melissa_layout_info": (C.c_int, [handle_t, p_i64, c_i32]),
     "melissa_impute": (C.c_int, [c_i32, c_i32, c_i32, c_i32, c_i32, p_dbl, c_dbl, p_dbl, p_dbl, c_i64, p_i64, p_i32,
                                  p_i32, p_dbl, p_dbl, c_i32]),
     "melissa_impute_noalloc": (C.c_int, [c_i32, c_i32, c_i32, c_i32, c_i32, p_dbl, c_dbl, p_dbl, p_dbl, c_i64, p_i64,

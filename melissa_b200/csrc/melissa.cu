@@ -24,6 +24,7 @@
 // is everything the M-step needs from the data (:368-373).
 #include "melissa_b200.h"
 #include "special.cuh"
+#include "fx128.cuh"
 
 #include <cuda_runtime.h>
 
@@ -73,7 +74,16 @@ struct BasisDev {
 
 // Small per-fit scalar block in device memory, all length-K arrays.
 struct Scalars {
-    double *beta, *delta0, *delta, *elogpi, *Eww, *Eww_acc, *pi, *logdet_acc, *lb_out;
+    double *beta, *delta0, *delta, *elogpi, *Eww, *pi, *logdet, *lb_out;
+    // cross-block sums, 128-bit fixed point so that they do not depend on block order (fx128.cuh):
+    // [E_ww K | log det 1 | colSums(r) K | sum r log r 1] pairs, then the "blocks done" counter of resp_kernel
+    unsigned long long *fx;
+    __host__ __device__ unsigned long long *fx_Eww(int k) const { return fx + 2 * k; }
+    __host__ __device__ unsigned long long *fx_logdet(int K) const { return fx + 2 * K; }
+    __host__ __device__ unsigned long long *fx_colsum(int K, int k) const { return fx + 2 * K + 2 + 2 * k; }
+    __host__ __device__ unsigned long long *fx_rlogr(int K) const { return fx + 4 * K + 2; }
+    __host__ __device__ unsigned long long *fx_done(int K) const { return fx + 4 * K + 4; }
+    static constexpr int fx_words(int K) { return 4 * K + 6; }
 };
 
 }  // namespace
@@ -101,7 +111,10 @@ struct melissa_handle {
     double alpha_0 = 0, beta_0 = 0, alpha_k = 0;
     double *U = nullptr;           // [M][K][R]
     double *Spk = nullptr;         // [M][K][T]
-    double *r = nullptr, *log_r = nullptr, *log_rho = nullptr;   // [N][K]
+    double *r = nullptr, *log_r = nullptr;                       // [N][K]
+    unsigned long long *log_rho_fx = nullptr;                    // [N][K][2] E-step sums, 128-bit fixed point (fx128.cuh)
+    unsigned long long *lb_fx = nullptr;                         // [4] lb_pz_qz partial (fixed point), wrong-side count
+    unsigned int *poison = nullptr;                              // a non-finite / out-of-range term was met
     double *red = nullptr;         // [M*K*R | K colsum | 1 sum r log r]
     int64_t red_len = 0;
     double *lbbuf = nullptr;       // [lb_pz_qz partial | #CpG with s*mu < -5]
@@ -116,7 +129,8 @@ struct melissa_handle {
     std::vector<cudaEvent_t> prof_ev;      // start/stop pairs
     std::vector<int> prof_id;
     Sliced *sl = nullptr;                  // v2 layout (sliced.cuh); null = v1 path
-    int sweep_grid[2][2] = {{0, 0}, {0, 0}};   // cached launch grid of the sweep variants (0 = not configured yet)
+    int sweep_cfg[2] = {0, 0};             // sweep variants whose function attributes have been set
+    int sweep_warps = 0;                   // warps per CTA of the sweep for this fit's K (0 = does not fit)
 };
 
 namespace {
@@ -198,8 +212,9 @@ __global__ void __launch_bounds__(128)
 sweep_kernel(const int64_t *__restrict__ pair_ptr, const int32_t *__restrict__ pair_cell,
              const int32_t *__restrict__ pair_region, const double *__restrict__ x,
              const uint8_t *__restrict__ y, double *__restrict__ stats, const double *__restrict__ U,
-             const double *__restrict__ r, double *__restrict__ log_rho, double *__restrict__ lbbuf,
-             int64_t P, int K, BasisDev basis) {
+             const double *__restrict__ r, unsigned long long *__restrict__ log_rho_fx,
+             unsigned long long *__restrict__ lb_fx, unsigned int *__restrict__ poison, int64_t P, int K,
+             BasisDev basis) {
     constexpr int T = D * (D + 1) / 2, R = D + T;
     __shared__ double red_smem[32];
     double lb_local = 0.0, wrong_side = 0.0;
@@ -278,17 +293,25 @@ sweep_kernel(const int64_t *__restrict__ pair_ptr, const int32_t *__restrict__ p
             double v = lin + trc;
             if (uniform) {
                 v = warp_sum(v);
-                if ((threadIdx.x & 31) == 0 && n0 >= 0) atomicAdd(&log_rho[(int64_t)n0 * K + k], v);
+                if ((threadIdx.x & 31) == 0 && n0 >= 0) {
+                    if (!(fabs(v) < FX_LIMIT)) atomicOr(poison, 1u);
+                    fx_add(log_rho_fx + 2 * ((int64_t)n0 * K + k), fx_from_double(v));
+                }
             } else if (valid) {
-                atomicAdd(&log_rho[(int64_t)n * K + k], v);
+                if (!(fabs(v) < FX_LIMIT)) atomicOr(poison, 1u);
+                fx_add(log_rho_fx + 2 * ((int64_t)n * K + k), fx_from_double(v));
             }
         }
     }
     if (WITH_LB) {
-        double s = block_sum(lb_local, red_smem);
-        if (threadIdx.x == 0) atomicAdd(&lbbuf[0], s);
-        s = block_sum(wrong_side, red_smem);
-        if (threadIdx.x == 0 && s != 0.0) atomicAdd(&lbbuf[1], s);
+        // per-thread sums are fixed by the launch shape; the cross-warp part is order-free
+        const double s0 = warp_sum(lb_local);
+        if ((threadIdx.x & 31) == 0) {
+            if (!(fabs(s0) < FX_LIMIT)) atomicOr(poison, 1u);
+            fx_add(lb_fx, fx_from_double(s0));
+        }
+        const double s = block_sum(wrong_side, red_smem);
+        if (threadIdx.x == 0 && s != 0.0) atomicAdd(lb_fx + 2, (unsigned long long)s);
     }
 }
 
@@ -298,39 +321,61 @@ sweep_kernel(const int64_t *__restrict__ pair_ptr, const int32_t *__restrict__ p
 // accumulators for the solve that follows.
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(128)
-resp_kernel(double *__restrict__ log_rho, const double *__restrict__ elogpi, double *__restrict__ r,
+resp_kernel(unsigned long long *__restrict__ log_rho_fx, const unsigned int *__restrict__ poison,
+            const double *__restrict__ elogpi, double *__restrict__ r,
             double *__restrict__ log_r, double *__restrict__ colsum, double *__restrict__ rlogr,
-            double *__restrict__ Eww_acc, double *__restrict__ logdet_acc, int N, int K) {
+            Scalars sc, int N, int K) {
     __shared__ double red_smem[32];
+    __shared__ bool is_last;
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
-    if (blockIdx.x == 0 && threadIdx.x < K) Eww_acc[threadIdx.x] = 0.0;
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        *logdet_acc = 0.0;
-        for (int k = blockDim.x; k < K; ++k) Eww_acc[k] = 0.0;
-    }
+    if (blockIdx.x == 0)
+        for (int i = threadIdx.x; i < 2 * K + 2; i += blockDim.x) sc.fx[i] = 0ull;     // E_ww and log det sums of the solve
     double lse = 0.0, rl = 0.0;
+    // a term the fixed-point sums could not hold (non-finite or >= 2^50) poisons the fit the way the
+    // reference's own arithmetic would: everything downstream becomes NaN
+    const double bias = *poison ? nan("") : 0.0;
+    auto rho = [&](int k) {
+        const unsigned long long *p = log_rho_fx + 2 * ((int64_t)n * K + k);
+        return fx_to_double(p[0], p[1]) + elogpi[k] + bias;
+    };
     if (n < N) {
         double mx = -INFINITY;
-        for (int k = 0; k < K; ++k) mx = fmax(mx, log_rho[(int64_t)n * K + k] + elogpi[k]);
+        for (int k = 0; k < K; ++k) mx = fmax(mx, rho(k));
         double s = 0.0;
-        for (int k = 0; k < K; ++k) s += exp(log_rho[(int64_t)n * K + k] + elogpi[k] - mx);
+        for (int k = 0; k < K; ++k) s += exp(rho(k) - mx);
         lse = log(s) + mx;                                     // R/utils.R:16-20
     }
     for (int k = 0; k < K; ++k) {
         double rk = 0.0;
         if (n < N) {
-            const double lr = log_rho[(int64_t)n * K + k] + elogpi[k] - lse;
+            const double lr = rho(k) - lse;
             rk = exp(lr);
             log_r[(int64_t)n * K + k] = lr;
             r[(int64_t)n * K + k] = rk;
-            log_rho[(int64_t)n * K + k] = 0.0;
             rl += rk * lr;
         }
         const double s = block_sum(rk, red_smem);
-        if (threadIdx.x == 0) atomicAdd(&colsum[k], s);
+        if (threadIdx.x == 0) fx_add(sc.fx_colsum(K, k), fx_from_double(s));
     }
+    if (n < N)
+        for (int k = 0; k < 2 * K; ++k) log_rho_fx[2 * (int64_t)n * K + k] = 0ull;       // ready for the next sweep
     const double s = block_sum(rl, red_smem);
-    if (threadIdx.x == 0) atomicAdd(rlogr, s);
+    if (threadIdx.x == 0) {
+        fx_add(sc.fx_rlogr(K), fx_from_double(s));
+        __threadfence();
+        is_last = atomicAdd(sc.fx_done(K), 1ull) == (unsigned long long)gridDim.x - 1;
+    }
+    __syncthreads();
+    if (is_last) {                       // the block that finishes last turns the sums into the doubles the all-reduce carries
+        __threadfence();
+        for (int k = threadIdx.x; k <= K; k += blockDim.x) {
+            unsigned long long *p = k < K ? sc.fx_colsum(K, k) : sc.fx_rlogr(K);
+            const double v = fx_to_double(__ldcg(p), __ldcg(p + 1));
+            if (k < K) colsum[k] = v; else *rlogr = v;
+            p[0] = p[1] = 0ull;
+        }
+        if (threadIdx.x == 0) *sc.fx_done(K) = 0ull;
+    }
 }
 
 // ---------------------------------------------------------------------------
@@ -396,8 +441,7 @@ contract_kernel(const int64_t *__restrict__ reg_ptr, const int32_t *__restrict__
 template <int D>
 __global__ void __launch_bounds__(128)
 solve_kernel(const double *__restrict__ acc, double *__restrict__ U, double *__restrict__ Spk,
-             const double *__restrict__ beta, double *__restrict__ Eww_acc,
-             double *__restrict__ logdet_acc, int M, int K, double alpha_k) {
+             const double *__restrict__ beta, Scalars sc, int M, int K, double alpha_k) {
     constexpr int T = D * (D + 1) / 2, R = D + T;
     __shared__ double red_smem[32];
     const int m = blockIdx.x * blockDim.x + threadIdx.x;
@@ -491,9 +535,9 @@ solve_kernel(const double *__restrict__ acc, double *__restrict__ U, double *__r
         }
     }
     double s = block_sum(eww, red_smem);
-    if (threadIdx.x == 0) atomicAdd(&Eww_acc[k], s);
+    if (threadIdx.x == 0) fx_add(sc.fx_Eww(k), fx_from_double(s));
     s = block_sum(logdetS, red_smem);
-    if (threadIdx.x == 0) atomicAdd(logdet_acc, s);
+    if (threadIdx.x == 0) fx_add(sc.fx_logdet(K), fx_from_double(s));
 }
 
 // Initial q(w): m = w0, S = solve(diag(50, D)) (R/melissa_vb.R:266-269, :279-280).
@@ -535,7 +579,7 @@ __global__ void scalars_kernel(Scalars sc, const double *__restrict__ colsum, in
             sc.delta[k] = sc.delta0[k];
             sc.pi[k] = 0.0;
         } else {
-            sc.Eww[k] = sc.Eww_acc[k];
+            sc.Eww[k] = fx_to_double(sc.fx_Eww(k)[0], sc.fx_Eww(k)[1]);
             double b = beta_0 + 0.5 * sc.Eww[k];
             if (b > 10.0 * alpha_k) b = 10.0 * alpha_k;
             sc.beta[k] = b;
@@ -546,6 +590,7 @@ __global__ void scalars_kernel(Scalars sc, const double *__restrict__ colsum, in
     }
     const double dsum = digamma_pos(sum_delta);
     for (int k = 0; k < K; ++k) sc.elogpi[k] = digamma_pos(sc.delta[k]) - dsum;
+    if (!init) *sc.logdet = fx_to_double(sc.fx_logdet(K)[0], sc.fx_logdet(K)[1]);
 }
 
 // Lower bound assembly (R/melissa_vb.R:475-492).  One thread.
@@ -574,7 +619,7 @@ __global__ void lb_kernel(Scalars sc, const double *__restrict__ colsum, const d
     }
     lb_p_pi += lgamma(sum_d0) - sum_lg0;
     lb_q_pi += lgamma(sum_dk) - sum_lgk;
-    const double lb_q_w = -0.5 * (*sc.logdet_acc) - 0.5 * D * (1.0 + LOG2PI) * (double)M * K;
+    const double lb_q_w = -0.5 * (*sc.logdet) - 0.5 * D * (1.0 + LOG2PI) * (double)M * K;
     const double lb_q_c = *rlogr;
     *sc.lb_out = lbbuf[0] + lb_p_c + lb_p_pi + lb_p_w + lb_p_tau - lb_q_c - lb_q_pi - lb_q_w - lb_q_tau;
 }
@@ -606,6 +651,22 @@ __global__ void impute_kernel(const int64_t *__restrict__ pair_ptr, const int32_
 }
 
 #include "sliced.cuh"
+#include "sweep3.cuh"
+
+// Per-lane values back into the caller's pair order: out[pair][d] = src[slice * 32 + lane][d], or, with
+// from_stats, the g = H^T E[z] part of the lane's record in the tile-ordered stats array.
+__global__ void lanes_to_pairs_kernel(const double *__restrict__ src, const int32_t *__restrict__ lane_pair,
+                                      double *__restrict__ out, int64_t n_lanes, int D, int R, int from_stats) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_lanes) return;
+    const int32_t p = lane_pair[t];
+    if (p < 0) return;
+    const int64_t s = t >> 5;
+    const int lane = (int)(t & 31);
+    for (int d = 0; d < D; ++d)
+        out[(int64_t)p * D + d] = from_stats ? src[s * ((int64_t)R * 32) + ((int64_t)(lane >> 2) * R + d) * 4 + (lane & 3)]
+                                             : src[t * D + d];
+}
 
 struct StageTimer {       // MELISSA_PACK_TIMING=1 prints where melissa_pack spends its time
     bool on = std::getenv("MELISSA_PACK_TIMING") != nullptr;
@@ -620,9 +681,11 @@ struct StageTimer {       // MELISSA_PACK_TIMING=1 prints where melissa_pack spe
 };
 
 // library-wide options (melissa_set_option)
-int g_opt_cell_block = 0;     // 0 = derive from g_opt_clusters_hint
-int g_opt_clusters_hint = 4;
-int g_opt_sliced = -1;   // -1 auto, 0 never, 1 require
+int g_opt_cell_block = 0;     // 0 = 256 cells
+int g_opt_sliced = -1;        // -1 auto, 0 never, 1 require
+int g_opt_sweep_chunk = 0;    // slices per chunk of the sweep, 0 = from the problem size
+int g_opt_sweep_group = 2;    // consecutive slices a warp claims at a time
+int g_opt_sweep_warps = 0;    // warps per CTA of the sweep, 0 = as many as fit
 
 void prof_begin(melissa_handle *h, int id) {
     h->launches++;
@@ -668,7 +731,7 @@ int launch_sweep(melissa_handle *h, bool with_lb, bool uniform_r) {
 #define SWEEP(LB_, UNI_)                                                                        \
     DISPATCH_D(h->D, sweep_kernel<DD, LB_, UNI_><<<grid, block, 0, h->stream>>>(                 \
                          h->pair_ptr, h->pair_cell, h->pair_region, h->x, h->y, h->stats, h->U, \
-                         h->r, h->log_rho, h->lbbuf, h->P, h->K, h->basis))
+                         h->r, h->log_rho_fx, h->lb_fx, h->poison, h->P, h->K, h->basis))
     if (with_lb && uniform_r) { SWEEP(true, true) }
     else if (with_lb) { SWEEP(true, false) }
     else if (uniform_r) { SWEEP(false, true) }
@@ -791,6 +854,18 @@ void build_slices_range(int cb_lo, int cb_hi, int Tn, int M, const int32_t *blk_
     }
 }
 
+// log2 of the RBF table's points per unit of x (sliced.cuh, rbf_row3), or -1 if gamma is too large for a
+// table of at most 2^13 + 3 entries.  The series there are cut where |w| = gamma s u_max stays below
+// w_max, which keeps their truncation error under 3e-16.
+int rbf_table_log2(const BasisDev &b) {
+    if (b.D <= 1) return 8;
+    const double u_max = std::max(std::fabs(-1.0 - b.mus[0]), std::fabs(1.0 - b.mus[0]));
+    const double w_max = b.D <= 9 ? 0.02 : 0.055;
+    for (int k = 8; k <= 12; ++k)
+        if (b.gamma * std::ldexp(1.0, -k) * u_max <= w_max) return k;
+    return -1;
+}
+
 bool rbf_equally_spaced(const BasisDev &b) {
     const int nb = b.D - 1;
     if (nb <= 1) return true;
@@ -806,9 +881,9 @@ void free_sliced(melissa_handle *h) {
     if (!sl) return;
     cudaFree(sl->x_sell); cudaFree(sl->ybits); cudaFree(sl->slice_xbase); cudaFree(sl->slice_ybase);
     cudaFree(sl->slice_len); cudaFree(sl->slice_region); cudaFree(sl->slice_cb); cudaFree(sl->lane_cell);
-    cudaFree(sl->lane_meta); cudaFree(sl->blk_cells); cudaFree(sl->reg_slice_ptr);
+    cudaFree(sl->lane_meta); cudaFree(sl->lane_pair); cudaFree(sl->blk_cells); cudaFree(sl->reg_slice_ptr);
     cudaFree(sl->reg_slice); cudaFree(sl->stats); cudaFree(sl->mills_tab); cudaFree(sl->rbf_tab);
-    cudaFree(sl->slice_counter);
+    cudaFree(sl->chunk_ptr); cudaFree(sl->chunk_counter);
     delete sl;
     h->sl = nullptr;
 }
@@ -829,16 +904,10 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
     Sliced *sl = new Sliced();
     h->sl = sl;
     StageTimer tm;
-    if (g_opt_cell_block > 0) {
-        sl->Tn = g_opt_cell_block;
-    } else {
-        // Largest multiple of 32 cells whose per-warp E-step sums (Tn x K doubles, 8 warps per CTA) still let
-        // three CTAs share an SM next to the two function tables: occupancy matters more to the sweep than
-        // the padding a smaller sorting window costs (measured at K = 4 and K = 10).
-        const int K = std::max(1, g_opt_clusters_hint), R = h->R;
-        const int budget = (75 * 1024 - 26 * 1024) / 8 / 8 - K * R;      // doubles per warp left for the sums
-        sl->Tn = std::max(32, std::min(128, (budget / K) / 32 * 32));
-    }
+    // Cells per block = the pool in which the pairs of one region are sorted by length before they are cut
+    // into slices: the larger, the less padding.  256 keeps the block's E-step sums (Tn x K x 16 bytes of
+    // shared memory in the sweep) affordable up to K ~ 24; beyond that the sweep runs with fewer warps.
+    sl->Tn = g_opt_cell_block > 0 ? g_opt_cell_block : 256;
     const int Tn = sl->Tn;
     sl->NB = (N + Tn - 1) / Tn;
     std::vector<int64_t> cell_ptr((size_t)N + 1, 0);
@@ -933,25 +1002,50 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
     std::vector<double2> rbf_tab;
     if (nb >= 1) {
         const double delta = nb >= 2 ? (b.mus[1] - b.mus[0]) : 1.0;
+        const int k = rbf_table_log2(b);               // grid spacing s = 2^-k (pack_impl has checked k >= 0)
+        rt.s = std::ldexp(1.0, -k);
+        rt.inv_s = std::ldexp(1.0, k);
+        rt.neg_s = -rt.s;
         rt.mu1 = b.mus[0];
-        rt.s = delta / RBF_SUB;
-        rt.inv_s = 1.0 / rt.s;
         rt.neg_gamma = -b.gamma;
+        rt.cA = -2.0 * b.gamma * rt.s;                 // -2 gamma u0 = cA j + cB,  u0 = j s - mu_1
+        rt.cB = 2.0 * b.gamma * rt.mu1;
         rt.g2d = 2.0 * b.gamma * delta;
         rt.q = std::exp(-b.gamma * delta * delta);
         rt.q2 = rt.q * rt.q;
-        const int k_lo = (int)std::floor((-1.0 - rt.mu1) * rt.inv_s) - 2, k_hi = (int)std::ceil((1.0 - rt.mu1) * rt.inv_s) + 2;
-        rt.idx0 = -k_lo;
-        rt.n_entries = k_hi - k_lo + 1;
+        const int j_hi = (1 << k) + 1;                 // x in [-1, 1] -> j in [-2^k, 2^k], one guard entry each side
+        rt.idx0 = j_hi;
+        rt.n_entries = 2 * j_hi + 1;
         rbf_tab.resize((size_t)rt.n_entries);
-        for (int k = k_lo; k <= k_hi; ++k) {
-            const double u0 = (double)k * rt.s;
-            rbf_tab[(size_t)(k - k_lo)] = make_double2(std::exp(-b.gamma * u0 * u0), rt.q * std::exp(rt.g2d * u0));
+        for (int j = -j_hi; j <= j_hi; ++j) {
+            const double u0 = (double)j * rt.s - rt.mu1;
+            rbf_tab[(size_t)(j + j_hi)] = make_double2(std::exp(-b.gamma * u0 * u0), rt.q * std::exp(rt.g2d * u0));
         }
     } else {
         rt = RbfTab{};
         rt.n_entries = 1;
         rbf_tab.assign(1, make_double2(1.0, 1.0));
+    }
+    // ---- chunks of the sweep: runs of consecutive slices that stay inside one cell block
+    std::vector<int32_t> chunk_ptr;
+    {
+        const int64_t target = g_opt_sweep_chunk > 0 ? g_opt_sweep_chunk
+                                                     : std::max<int64_t>(48, std::min<int64_t>(2048, S / ((int64_t)h->sm_count * 16)));
+        int64_t s0 = 0;
+        for (int t = 0; t < nthr; ++t) {
+            const auto &cbv = parts[(size_t)t].slice_cb;
+            size_t q = 0;
+            while (q < cbv.size()) {
+                size_t e = q;
+                while (e < cbv.size() && cbv[e] == cbv[q]) ++e;          // [q, e): the slices of one cell block
+                const int64_t n = (int64_t)(e - q), pieces = std::max<int64_t>(1, (n + target - 1) / target);
+                for (int64_t c = 0; c < pieces; ++c) chunk_ptr.push_back((int32_t)(s0 + (int64_t)q + n * c / pieces));
+                q = e;
+            }
+            s0 += (int64_t)cbv.size();
+        }
+        chunk_ptr.push_back((int32_t)S);
+        sl->NC = (int)chunk_ptr.size() - 1;
     }
     tm.lap("region index + tables");
     // ---- upload, piece by piece
@@ -960,7 +1054,8 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
     if ((rc = dev_alloc(&sl->slice_xbase, S)) || (rc = dev_alloc(&sl->slice_ybase, S)) ||
         (rc = dev_alloc(&sl->slice_len, S)) || (rc = dev_alloc(&sl->slice_region, S)) ||
         (rc = dev_alloc(&sl->slice_cb, S)) || (rc = dev_alloc(&sl->lane_cell, S * 32)) ||
-        (rc = dev_alloc(&sl->lane_meta, S * 32)) || (rc = dev_alloc(&d_src, S * 32)) ||
+        (rc = dev_alloc(&sl->lane_meta, S * 32)) || (rc = dev_alloc(&sl->lane_pair, S * 32)) ||
+        (rc = dev_alloc(&d_src, S * 32)) || (rc = upload(&sl->chunk_ptr, chunk_ptr)) ||
         (rc = upload(&sl->blk_cells, blk_cells)) || (rc = upload(&sl->reg_slice_ptr, reg_slice_ptr)) ||
         (rc = upload(&sl->reg_slice, reg_slice)) || (rc = upload(&sl->rbf_tab, rbf_tab))) {
         cudaFree(d_src);
@@ -985,17 +1080,18 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
         PUT(sl->slice_cb, pt.slice_cb, 1, int32_t)
         PUT(sl->lane_cell, pt.lane_cell, 32, int32_t)
         PUT(sl->lane_meta, pt.lane_meta, 32, int32_t)
+        PUT(sl->lane_pair, pt.lane_pair, 32, int32_t)
         PUT(d_src, pt.lane_src, 32, int64_t)
 #undef PUT
     }
     // + 2 prefetch groups of slack: the sweep reads one group past the end of every slice
-    if ((rc = dev_alloc(&sl->x_sell, sl->x_len + 2 * SWEEP_XU * 32)) || (rc = dev_alloc(&sl->ybits, sl->y_len)) ||
+    if ((rc = dev_alloc(&sl->x_sell, sl->x_len + 2 * SWEEP3_XU * 32)) || (rc = dev_alloc(&sl->ybits, sl->y_len)) ||
         (rc = dev_alloc(&sl->stats, S * h->R * 32)) || (rc = dev_alloc(&sl->mills_tab, MILLS_N)) ||
-        (rc = dev_alloc(&sl->slice_counter, 1))) {
+        (rc = dev_alloc(&sl->chunk_counter, 1))) {
         cudaFree(d_src);
         return rc;
     }
-    cudaMemsetAsync(sl->x_sell + sl->x_len, 0, (size_t)2 * SWEEP_XU * 32 * sizeof(double), nullptr);
+    cudaMemsetAsync(sl->x_sell + sl->x_len, 0, (size_t)2 * SWEEP3_XU * 32 * sizeof(double), nullptr);
     tm.lap("upload index arrays");
     const int grid = (int)((S * 32 + 255) / 256);
     sell_fill_kernel<<<grid, 256>>>(h->x, h->y, d_src, sl->lane_meta, sl->slice_xbase, sl->slice_ybase, sl->slice_len,
@@ -1014,65 +1110,63 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
     cudaFree(d_src);
     if (e != cudaSuccess) return fail(MELISSA_ERR_CUDA, "sliced layout build failed: %s", cudaGetErrorString(e));
     tm.lap("fill + HtH kernels");
-    sl->lane_pair.resize((size_t)nthr);
-    for (int t = 0; t < nthr; ++t) sl->lane_pair[(size_t)t] = std::move(parts[(size_t)t].lane_pair);
     sl->on = true;
     return MELISSA_OK;
 }
 
-size_t sweep_v2_smem(const melissa_handle *h, int nw) {
+// Shared memory of one sweep CTA with nw warps: the two tables, the block's fixed-point sums,
+// one U[m] staging area per warp, lb sums and control words.
+size_t sweep3_smem(const melissa_handle *h, int nw) {
     const Sliced *sl = h->sl;
-    return (size_t)sl->rt.n_entries * sizeof(double2) +
-           ((size_t)MILLS_N + 1 + (size_t)sl->Tn * h->K * nw + (SWEEP_STAGE_U ? (size_t)nw * h->K * h->R : 0)) * sizeof(double);
+    const size_t UR = ((size_t)h->K * h->R + 1) & ~(size_t)1;
+    return (size_t)sl->rt.n_entries * sizeof(double2) + ((size_t)MILLS_N + 1) * sizeof(double) +
+           2 * (size_t)sl->Tn * h->K * sizeof(unsigned long long) + (size_t)nw * UR * sizeof(double) + 4 * 8 + 16;
 }
 
-int sweep_v2_warps(const melissa_handle *h) {
-    for (int nw : {8, 4, 2, 1})
-        if (sweep_v2_smem(h, nw) <= (nw >= 4 ? 100u * 1024 : 220u * 1024)) return nw;
-    for (int nw : {4, 2, 1})
-        if (sweep_v2_smem(h, nw) <= 220u * 1024) return nw;
+// Most warps (of SWEEP3_THREADS / 32) whose staging areas still fit next to the rest; 0 = not even four.
+int sweep3_warps(const melissa_handle *h) {
+    int nw = SWEEP3_THREADS / 32;
+    if (g_opt_sweep_warps > 0) nw = std::min(nw, g_opt_sweep_warps);
+    for (; nw >= 4; nw -= 2)
+        if (sweep3_smem(h, nw) <= 227u * 1024) return nw;
     return 0;
 }
 
-int launch_sweep_v2(melissa_handle *h, bool with_lb, bool uniform_r) {
+__global__ void fill_kernel(double *p, int64_t n, double v) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
+}
+
+int launch_sweep3(melissa_handle *h, bool with_lb) {
     Sliced *sl = h->sl;
-    const int nw = sweep_v2_warps(h);
-    if (nw == 0) return fail(MELISSA_ERR_ARG, "K = %d needs more shared memory than one SM has; lower the cell block", h->K);
-    const size_t smem = sweep_v2_smem(h, nw);
-    SweepV2Args a;
+    const int nw = h->sweep_warps;
+    if (nw == 0)
+        return fail(MELISSA_ERR_ARG, "K = %d with cell blocks of %d does not fit the sweep's shared memory; "
+                    "pack with a smaller \"cell_block\" option", h->K, sl->Tn);
+    const size_t smem = sweep3_smem(h, nw);
+    Sweep3Args a;
     a.x_sell = sl->x_sell; a.ybits = sl->ybits; a.slice_xbase = sl->slice_xbase; a.slice_ybase = sl->slice_ybase;
     a.slice_len = sl->slice_len; a.slice_region = sl->slice_region; a.slice_cb = sl->slice_cb;
     a.lane_cell = sl->lane_cell; a.lane_meta = sl->lane_meta; a.blk_cells = sl->blk_cells;
-    a.stats = sl->stats; a.U = h->U; a.r = h->r; a.log_rho = h->log_rho; a.lbbuf = h->lbbuf;
-    a.mills_tab = sl->mills_tab; a.rbf_tab = sl->rbf_tab; a.rt = sl->rt;
-    a.basis = h->basis; a.K = h->K; a.Tn = sl->Tn; a.N = h->N;
-    a.slice_counter = sl->slice_counter; a.S = sl->S;
+    a.chunk_ptr = sl->chunk_ptr; a.stats = sl->stats; a.U = h->U; a.r = h->r;
+    a.log_rho_fx = h->log_rho_fx; a.lb_fx = h->lb_fx; a.poison = h->poison;
+    a.mills_tab = sl->mills_tab; a.rbf_tab = sl->rbf_tab; a.rt = sl->rt; a.basis = h->basis;
+    a.K = h->K; a.Tn = sl->Tn; a.NC = sl->NC; a.G = std::max(1, g_opt_sweep_group);
+    a.chunk_counter = sl->chunk_counter;
     const int block = 32 * nw;
-    int grid = 1;
-    CU(cudaMemsetAsync(sl->slice_counter, 0, sizeof(unsigned long long), h->stream));
-    if (with_lb) CU(cudaMemsetAsync(h->lbbuf, 0, 2 * sizeof(double), h->stream));
+    const int grid = std::min(h->sm_count, sl->NC);
+    CU(cudaMemsetAsync(sl->chunk_counter, 0, sizeof(unsigned int), h->stream));
     prof_begin(h, MELISSA_KERNEL_SWEEP);
-#define SWEEP2(LB_, UNI_)                                                                                   \
+#define SWEEP3(LB_)                                                                                         \
     DISPATCH_D(h->D, {                                                                                      \
-        auto kfn = sweep_v2_kernel<DD, LB_, UNI_>;                                                          \
-        int &cached = h->sweep_grid[LB_ ? 1 : 0][UNI_ ? 1 : 0];   /* attributes / occupancy: once per fit */ \
-        if (cached == 0) {                                                                                  \
-            /* the opt-in limit is per function, not per handle: ask for the most any fit can need */     \
+        auto kfn = sweep3_kernel<DD, LB_>;                                                                  \
+        if (!h->sweep_cfg[LB_ ? 1 : 0]) {      /* the opt-in limit is per function: ask for the most any fit can need */ \
             CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));         \
-            CU(cudaFuncSetAttribute(kfn, cudaFuncAttributePreferredSharedMemoryCarveout, 100));             \
-            int per_sm = 1;                                                                                 \
-            CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, block, smem));                   \
-            cached = (int)std::min<int64_t>((sl->S + nw - 1) / nw, (int64_t)h->sm_count * std::max(1, per_sm)); \
+            h->sweep_cfg[LB_ ? 1 : 0] = 1;                                                                  \
         }                                                                                                   \
-        grid = cached;                                                                                      \
-        a.chunk = std::max<int64_t>(1, std::min<int64_t>(64, sl->S / ((int64_t)grid * nw * 4)));            \
         kfn<<<grid, block, smem, h->stream>>>(a);                                                           \
     })
-    if (with_lb && uniform_r) { SWEEP2(true, true) }
-    else if (with_lb) { SWEEP2(true, false) }
-    else if (uniform_r) { SWEEP2(false, true) }
-    else { SWEEP2(false, false) }
-#undef SWEEP2
+    if (with_lb) { SWEEP3(true) } else { SWEEP3(false) }
+#undef SWEEP3
     prof_end(h);
     CU(cudaGetLastError());
     return MELISSA_OK;
@@ -1123,9 +1217,11 @@ int launch_contract_v2(melissa_handle *h) {
 }
 
 void free_fit(melissa_handle *h) {
-    cudaFree(h->U); cudaFree(h->Spk); cudaFree(h->r); cudaFree(h->log_r); cudaFree(h->log_rho);
-    cudaFree(h->red); cudaFree(h->lbbuf); cudaFree(h->scal_mem);
-    h->U = h->Spk = h->r = h->log_r = h->log_rho = h->red = h->lbbuf = h->scal_mem = nullptr;
+    cudaFree(h->U); cudaFree(h->Spk); cudaFree(h->r); cudaFree(h->log_r); cudaFree(h->log_rho_fx);
+    cudaFree(h->red); cudaFree(h->lbbuf); cudaFree(h->scal_mem); cudaFree(h->lb_fx);
+    h->U = h->Spk = h->r = h->log_r = h->red = h->lbbuf = h->scal_mem = nullptr;
+    h->log_rho_fx = h->lb_fx = nullptr;
+    h->poison = nullptr;
     h->begun = false;
 }
 
@@ -1248,10 +1344,11 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
     for (int32_t m = 0; m < n_regions; ++m) reg_cnt[(size_t)m + 1] += reg_cnt[m];
     BasisDev basis_chk{};
     basis_chk.D = n_basis + 1;
+    basis_chk.gamma = gamma;
     for (int j = 0; j < n_basis && j < MAX_MUS; ++j) basis_chk.mus[j] = mus[j];
-    const bool use_sliced = g_opt_sliced != 0 && rbf_equally_spaced(basis_chk);
+    const bool use_sliced = g_opt_sliced != 0 && rbf_equally_spaced(basis_chk) && rbf_table_log2(basis_chk) >= 0;
     if (g_opt_sliced == 1 && !use_sliced)
-        return fail(MELISSA_ERR_ARG, "the sliced path needs equally spaced RBF centres");
+        return fail(MELISSA_ERR_ARG, "the sliced path needs equally spaced RBF centres (and a gamma its table can resolve)");
     std::vector<int32_t> reg_pair, reg_cell;
     if (!use_sliced) {
         reg_pair.resize((size_t)P);
@@ -1360,7 +1457,7 @@ int melissa_profiles_mle(melissa_handle *h, double lambda, int32_t n_iter, doubl
     int rc = dev_alloc(&d_out, sl->S * 32 * D);
     if (rc) return rc;
     const size_t smem = (size_t)sl->rt.n_entries * sizeof(double2) + ((size_t)MILLS_N + 1) * sizeof(double);
-    const int grid = (int)std::min<int64_t>((sl->S + 7) / 8, (int64_t)h->sm_count * 4);
+    const int grid = (int)std::min<int64_t>((sl->S + 7) / 8, (int64_t)h->sm_count * 2);
     auto run = [&]() -> int {
         DISPATCH_D(D, {
             auto kfn = mle_kernel<DD>;
@@ -1372,18 +1469,16 @@ int melissa_profiles_mle(melissa_handle *h, double lambda, int32_t n_iter, doubl
         return MELISSA_OK;
     };
     if ((rc = run())) { cudaFree(d_out); return rc; }
-    h->launches++;
-    std::vector<double> buf((size_t)sl->S * 32 * D);
-    const cudaError_t e = cudaMemcpy(buf.data(), d_out, buf.size() * sizeof(double), cudaMemcpyDeviceToHost);
+    double *d_pairs = nullptr;
+    if ((rc = dev_alloc(&d_pairs, h->P * D))) { cudaFree(d_out); return rc; }
+    lanes_to_pairs_kernel<<<(unsigned)((sl->S * 32 + 255) / 256), 256, 0, h->stream>>>(d_out, sl->lane_pair, d_pairs,
+                                                                                         sl->S * 32, D, h->R, 0);
+    h->launches += 2;
+    cudaError_t e = cudaMemcpyAsync(w_out, d_pairs, (size_t)h->P * D * sizeof(double), cudaMemcpyDeviceToHost, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
     cudaFree(d_out);
+    cudaFree(d_pairs);
     if (e != cudaSuccess) return fail(MELISSA_ERR_CUDA, "melissa_profiles_mle failed: %s", cudaGetErrorString(e));
-    int64_t q = 0;
-    for (const auto &piece : sl->lane_pair)
-        for (size_t i = 0; i < piece.size(); ++i, ++q) {
-            const int32_t p = piece[i];
-            if (p < 0) continue;
-            for (int d = 0; d < D; ++d) w_out[(size_t)p * D + d] = buf[(size_t)q * D + d];
-        }
     return MELISSA_OK;
 }
 
@@ -1394,9 +1489,20 @@ int melissa_set_option(const char *key, int64_t value) {
         g_opt_cell_block = (int)value;
         return MELISSA_OK;
     }
-    if (!std::strcmp(key, "clusters_hint")) {
-        if (value < 1 || value > 64) return fail(MELISSA_ERR_ARG, "clusters_hint must be in 1..64");
-        g_opt_clusters_hint = (int)value;
+    if (!std::strcmp(key, "clusters_hint")) return MELISSA_OK;      // round-1 knob: the layout no longer depends on K
+    if (!std::strcmp(key, "sweep_chunk")) {
+        if (value < 0 || value > (1 << 20)) return fail(MELISSA_ERR_ARG, "sweep_chunk must be in 0..2^20");
+        g_opt_sweep_chunk = (int)value;
+        return MELISSA_OK;
+    }
+    if (!std::strcmp(key, "sweep_group")) {
+        if (value < 1 || value > 64) return fail(MELISSA_ERR_ARG, "sweep_group must be in 1..64");
+        g_opt_sweep_group = (int)value;
+        return MELISSA_OK;
+    }
+    if (!std::strcmp(key, "sweep_warps")) {
+        if (value < 0 || value > SWEEP3_THREADS / 32) return fail(MELISSA_ERR_ARG, "sweep_warps must be in 0..%d", SWEEP3_THREADS / 32);
+        g_opt_sweep_warps = (int)value;
         return MELISSA_OK;
     }
     if (!std::strcmp(key, "contract_mma")) {
@@ -1462,7 +1568,6 @@ int melissa_vb_begin(melissa_handle *h, int32_t K, const double *w0, const doubl
         if (!(delta_0[k] > 0.0)) return fail(MELISSA_ERR_ARG, "delta_0 must be positive");
     CU(cudaSetDevice(h->device));
     free_fit(h);
-    for (auto &row : h->sweep_grid) row[0] = row[1] = 0;
     h->K = K;
     h->stream = (cudaStream_t)stream;
     h->N_total = n_cells_total;
@@ -1476,18 +1581,23 @@ int melissa_vb_begin(melissa_handle *h, int32_t K, const double *w0, const doubl
     if ((rc = dev_alloc(&h->Spk, MK * h->T))) return rc;
     if ((rc = dev_alloc(&h->r, (int64_t)h->N * K))) return rc;
     if ((rc = dev_alloc(&h->log_r, (int64_t)h->N * K))) return rc;
-    if ((rc = dev_alloc(&h->log_rho, (int64_t)h->N * K))) return rc;
+    if ((rc = dev_alloc(&h->log_rho_fx, (int64_t)h->N * K * 2))) return rc;
+    if ((rc = dev_alloc(&h->lb_fx, 6))) return rc;
+    h->poison = reinterpret_cast<unsigned int *>(h->lb_fx + 4);
     h->red_len = MK * h->R + K + 1;
     if ((rc = dev_alloc(&h->red, h->red_len))) return rc;
     if ((rc = dev_alloc(&h->lbbuf, 2))) return rc;
-    if ((rc = dev_alloc(&h->scal_mem, (int64_t)7 * K + 2))) return rc;
+    const int64_t n_scal = (int64_t)6 * K + 2 + Scalars::fx_words(K);
+    if ((rc = dev_alloc(&h->scal_mem, n_scal))) return rc;
     double *s = h->scal_mem;
     h->sc.beta = s; h->sc.delta0 = s + K; h->sc.delta = s + 2 * K; h->sc.elogpi = s + 3 * K;
-    h->sc.Eww = s + 4 * K; h->sc.Eww_acc = s + 5 * K; h->sc.pi = s + 6 * K;
-    h->sc.logdet_acc = s + 7 * K; h->sc.lb_out = s + 7 * K + 1;
+    h->sc.Eww = s + 4 * K; h->sc.pi = s + 5 * K;
+    h->sc.logdet = s + 6 * K; h->sc.lb_out = s + 6 * K + 1;
+    h->sc.fx = reinterpret_cast<unsigned long long *>(s + 6 * K + 2);
     cudaStream_t st = h->stream;
-    CU(cudaMemsetAsync(h->scal_mem, 0, ((size_t)7 * K + 2) * sizeof(double), st));
-    CU(cudaMemsetAsync(h->log_rho, 0, (size_t)h->N * K * sizeof(double), st));
+    CU(cudaMemsetAsync(h->scal_mem, 0, (size_t)n_scal * sizeof(double), st));
+    CU(cudaMemsetAsync(h->log_rho_fx, 0, (size_t)h->N * K * 2 * sizeof(unsigned long long), st));
+    CU(cudaMemsetAsync(h->lb_fx, 0, 6 * sizeof(unsigned long long), st));
     CU(cudaMemsetAsync(h->r, 0, (size_t)h->N * K * sizeof(double), st));
     CU(cudaMemsetAsync(h->log_r, 0, (size_t)h->N * K * sizeof(double), st));
     CU(cudaMemsetAsync(h->red, 0, (size_t)h->red_len * sizeof(double), st));
@@ -1509,12 +1619,15 @@ int melissa_vb_begin(melissa_handle *h, int32_t K, const double *w0, const doubl
     h->launches++;
     CU(cudaGetLastError());
     h->begun = true;
-    if (h->sl) {
-        if (sweep_v2_warps(h) == 0)
-            return fail(MELISSA_ERR_ARG, "K = %d does not fit the sweep's shared memory at cell block %d", K, h->sl->Tn);
-    }
     // mu from rowMeans(w), E[z], E-step terms for i = 2  (R/melissa_vb.R:283-302)
-    return h->sl ? launch_sweep_v2(h, false, true) : launch_sweep(h, false, true);
+    if (h->sl) {
+        h->sweep_warps = sweep3_warps(h);
+        // rowMeans over clusters = responsibilities 1/K for every cell in this first sweep
+        fill_kernel<<<grid_for((int64_t)h->N * K, 256, h->sm_count, 8), 256, 0, st>>>(h->r, (int64_t)h->N * K, 1.0 / (double)K);
+        h->launches++;
+        return launch_sweep3(h, false);
+    }
+    return launch_sweep(h, false, true);
 }
 
 int melissa_vb_phase_a(melissa_handle *h) {
@@ -1524,8 +1637,8 @@ int melissa_vb_phase_a(melissa_handle *h) {
     CU(cudaMemsetAsync(h->red, 0, (size_t)h->red_len * sizeof(double), h->stream));
     double *colsum = h->red + MK * h->R, *rlogr = colsum + h->K;
     prof_begin(h, MELISSA_KERNEL_RESP);
-    resp_kernel<<<(h->N + 127) / 128, 128, 0, h->stream>>>(h->log_rho, h->sc.elogpi, h->r, h->log_r, colsum,
-                                                              rlogr, h->sc.Eww_acc, h->sc.logdet_acc, h->N, h->K);
+    resp_kernel<<<(h->N + 127) / 128, 128, 0, h->stream>>>(h->log_rho_fx, h->poison, h->sc.elogpi, h->r, h->log_r,
+                                                              colsum, rlogr, h->sc, h->N, h->K);
     prof_end(h);
     CU(cudaGetLastError());
     return h->sl ? launch_contract_v2(h) : launch_contract(h);
@@ -1540,8 +1653,7 @@ int melissa_vb_phase_b(melissa_handle *h, int32_t with_lb) {
         const dim3 grid((h->M + 127) / 128, h->K);
         auto run = [&]() -> int {
             DISPATCH_D(h->D, solve_kernel<DD><<<grid, 128, 0, h->stream>>>(
-                                 h->red, h->U, h->Spk, h->sc.beta, h->sc.Eww_acc, h->sc.logdet_acc, h->M, h->K,
-                                 h->alpha_k));
+                                 h->red, h->U, h->Spk, h->sc.beta, h->sc, h->M, h->K, h->alpha_k));
             return MELISSA_OK;
         };
         int rc;
@@ -1553,9 +1665,14 @@ int melissa_vb_phase_b(melissa_handle *h, int32_t with_lb) {
     scalars_kernel<<<1, 32, 0, h->stream>>>(h->sc, colsum, h->K, h->alpha_k, h->beta_0, (double)h->N_total, 0);
     prof_end(h);
     CU(cudaGetLastError());
-    if (h->sl) return launch_sweep_v2(h, with_lb != 0, false);
-    if (with_lb) CU(cudaMemsetAsync(h->lbbuf, 0, 2 * sizeof(double), h->stream));
-    return launch_sweep(h, with_lb != 0, false);
+    int rc = h->sl ? launch_sweep3(h, with_lb != 0) : launch_sweep(h, with_lb != 0, false);
+    if (rc) return rc;
+    if (with_lb) {                      // this shard's lb_pz_qz as a double, ready for the all-reduce
+        lb_finish_kernel<<<1, 32, 0, h->stream>>>(h->lb_fx, h->lbbuf);
+        h->launches++;
+        CU(cudaGetLastError());
+    }
+    return MELISSA_OK;
 }
 
 int melissa_vb_lower_bound(melissa_handle *h, double *lb_out) {
@@ -1597,6 +1714,14 @@ int melissa_sync(melissa_handle *h) {
 }
 
 int64_t melissa_launch_count(const melissa_handle *h) { return h ? h->launches : 0; }
+
+int melissa_layout_info(const melissa_handle *h, int64_t *out, int32_t n) {
+    if (!h || !out) return fail(MELISSA_ERR_ARG, "handle / out is NULL");
+    const int64_t v[8] = {h->sl ? 1 : 0, h->sl ? h->sl->Tn : 0, h->sl ? h->sl->S : 0, h->sl ? h->sl->x_len : h->nnz,
+                          h->nnz, h->P, h->sl ? h->sl->NC : 0, h->sl ? h->sweep_warps : 0};
+    for (int i = 0; i < n && i < 8; ++i) out[i] = v[i];
+    return MELISSA_OK;
+}
 
 int melissa_vb_fetch(melissa_handle *h, double *W, double *W_Sigma, double *r_nk, double *delta,
                      double *alpha, double *beta, double *pi_k) {
@@ -1649,18 +1774,16 @@ int melissa_vb_fetch_HtEz(melissa_handle *h, double *out) {
     CU(cudaStreamSynchronize(h->stream));
     if (h->sl) {
         const Sliced *sl = h->sl;
-        const size_t rec = (size_t)h->R * 32;
-        std::vector<double> buf((size_t)sl->S * rec);
-        CU(cudaMemcpy(buf.data(), sl->stats, buf.size() * sizeof(double), cudaMemcpyDeviceToHost));
-        int64_t q = 0;
-        for (const auto &piece : sl->lane_pair)
-            for (size_t i = 0; i < piece.size(); i += 32, ++q)
-                for (int l = 0; l < 32; ++l) {
-                    const int32_t p = piece[i + l];
-                    if (p < 0) continue;
-                    for (int d = 0; d < h->D; ++d)
-                        out[(size_t)p * h->D + d] = buf[(size_t)q * rec + ((size_t)(l >> 2) * h->R + d) * 4 + (l & 3)];
-                }
+        double *d_pairs = nullptr;
+        int rc = dev_alloc(&d_pairs, h->P * h->D);
+        if (rc) return rc;
+        lanes_to_pairs_kernel<<<(unsigned)((sl->S * 32 + 255) / 256), 256, 0, h->stream>>>(sl->stats, sl->lane_pair, d_pairs,
+                                                                                             sl->S * 32, h->D, h->R, 1);
+        h->launches++;
+        cudaError_t e = cudaMemcpyAsync(out, d_pairs, (size_t)h->P * h->D * sizeof(double), cudaMemcpyDeviceToHost, h->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+        cudaFree(d_pairs);
+        if (e != cudaSuccess) return fail(MELISSA_ERR_CUDA, "melissa_vb_fetch_HtEz failed: %s", cudaGetErrorString(e));
         return MELISSA_OK;
     }
     CU(cudaMemcpy2D(out, (size_t)h->D * sizeof(double), h->stats, (size_t)h->R * sizeof(double),

@@ -16,28 +16,22 @@
 #pragma once
 
 struct RbfTab {
-    double mu1, s, inv_s, neg_gamma, g2d, q, q2;
+    double inv_s, neg_s, neg_gamma, cA, cB, g2d, q2;
+    double s, mu1, q;
     int n_entries, idx0;
 };
 
-constexpr int MILLS_SP = 128;                 // table points per unit of t
+constexpr int MILLS_SP = 512;                 // table points per unit of t
 constexpr int MILLS_HALF = 8 * MILLS_SP;      // t in [-8, 8]
 constexpr int MILLS_N = 2 * MILLS_HALF + 1;
-#ifndef SWEEP_XU
-#define SWEEP_XU 2
-#endif
-#ifndef SWEEP_MINB
-#define SWEEP_MINB 3
-#endif
-#ifndef SWEEP_STAGE_U
-#define SWEEP_STAGE_U 1     // 1: copy U[m] to shared memory per slice; 0: read it through L1 (uniform loads)
-#endif
-constexpr int RBF_SUB = 128;                  // table points per centre spacing
 constexpr double MAGIC = 6755399441055744.0;  // 1.5 * 2^52: (v + MAGIC) - MAGIC rounds v to an integer
+#ifndef SWEEP3_THREADS
+#define SWEEP3_THREADS 768                    // one persistent CTA per SM
+#endif
 
 struct Sliced {
     bool on = false;
-    int Tn = 128, NB = 0;
+    int Tn = 256, NB = 0;
     int64_t S = 0, x_len = 0, y_len = 0;
     double *x_sell = nullptr;
     uint32_t *ybits = nullptr;
@@ -46,6 +40,7 @@ struct Sliced {
     int32_t *slice_cb = nullptr;          // [S] cell block of the slice
     int32_t *lane_cell = nullptr;         // [S*32] global cell index, -1 = padding lane
     int32_t *lane_meta = nullptr;         // [S*32] CpG count | (position of the cell in its block << 16)
+    int32_t *lane_pair = nullptr;         // [S*32] pair (in the caller's order) of the lane, -1 = padding lane
     int32_t *blk_cells = nullptr;         // [NB*Tn] global cell index of each block position, -1 = none
     int64_t *reg_slice_ptr = nullptr;     // [M + 1]
     int32_t *reg_slice = nullptr;         // [S]
@@ -53,8 +48,9 @@ struct Sliced {
     double *mills_tab = nullptr;          // [MILLS_N]
     double2 *rbf_tab = nullptr;           // [rt.n_entries] (E(u0), q B(u0))
     RbfTab rt{};
-    unsigned long long *slice_counter = nullptr;   // slice dispenser of the persistent sweep
-    std::vector<std::vector<int32_t>> lane_pair;   // host, per build piece: original pair of (slice, lane), -1 = padding
+    int32_t *chunk_ptr = nullptr;         // [NC + 1] first slice of each chunk of the sweep
+    int NC = 0;
+    unsigned int *chunk_counter = nullptr;         // chunk dispenser of the persistent sweep
 };
 
 // R(t0) = Phi(t0) / phi(t0) on the grid t0 = (i - MILLS_HALF) / MILLS_SP.
@@ -68,157 +64,84 @@ __global__ void mills_table_kernel(double *tab) {
     tab[i] = R;
 }
 
-// E[z | z > 0], z ~ N(t, 1), from the table: R = Phi/phi satisfies R' = 1 + t R, so all
-// Taylor coefficients about a grid point follow from R(t0) alone:
-//   c_0 = R0, c_1 = 1 + t0 R0, c_{n+1} = (c_{n-1} + t0 c_n) / (n + 1).
-// Order 5 at spacing 1/128 is at the rounding floor: against mpmath it is indistinguishable from order 6
-// and from the erfcx closed form (order 4 would lose a digit: 5e-14); tests/test_table_functions.py.
-__device__ __forceinline__ double trunc_mean_tab(double t, const double *__restrict__ tab) {
-    if (!(fabs(t) < 7.99)) return trunc_mean(t);
-    const double v = fma(t, (double)MILLS_SP, MAGIC);
-    const int i = __double2loint(v);
-    const double t0 = (v - MAGIC) * (1.0 / MILLS_SP);
-    const double d = t - t0;
-    const double R0 = tab[i + MILLS_HALF];
-    const double c1 = fma(t0, R0, 1.0);
-    const double c2 = 0.5 * fma(t0, c1, R0);
-    const double c3 = (1.0 / 3.0) * fma(t0, c2, c1);
-    const double c4 = 0.25 * fma(t0, c3, c2);
-    const double c5 = 0.2 * fma(t0, c4, c3);
-    double R = fma(d, c5, c4);
-    R = fma(d, R, c3);
-    R = fma(d, R, c2);
-    R = fma(d, R, c1);
-    R = fma(d, R, R0);
-    return t + __drcp_rn(R);
-}
-
-// RBF row from the position, equally spaced centres mu_j = mu_1 + (j-1) Delta:
-//   h_1 = exp(-gamma u^2),  h_{j+1} = h_j * b * q^(2j-1),  u = x - mu_1,   (the table stores q b)
-//   b = exp(2 gamma Delta u), q = exp(-gamma Delta^2).
-// exp(-gamma u^2) and b come from a table at u0 = k s (s = Delta / RBF_SUB) times short
-// series in the remainder d = u - u0 (|arguments| < 0.05).
-template <int D>
-__device__ __forceinline__ void eval_basis_tab(double x, const RbfTab &rt, const double2 *__restrict__ tab,
-                                               const BasisDev &basis, double (&h)[D]) {
-    h[0] = 1.0;
-    if (D == 1) return;
-    const double u = x - rt.mu1;
-    const double v = fma(u, rt.inv_s, MAGIC);
-    const int idx = __double2loint(v) + rt.idx0;
-    const double u0 = (v - MAGIC) * rt.s;
-    const double d = u - u0;
-    if ((unsigned)idx >= (unsigned)rt.n_entries) {           // x outside [-1, 1]: plain evaluation
-        eval_basis<D>(x, basis, h);
-        return;
-    }
-    const double2 eb = tab[idx];
-    const double w = (rt.neg_gamma * d) * fma(2.0, u0, d);   // -gamma (2 u0 d + d^2)
-    double c = fma(w, 1.0 / 5040, 1.0 / 720);
-    c = fma(w, c, 1.0 / 120);
-    c = fma(w, c, 1.0 / 24);
-    c = fma(w, c, 1.0 / 6);
-    c = fma(w, c, 0.5);
-    c = fma(w, c, 1.0);
-    c = fma(w, c, 1.0);
-    h[1] = eb.x * c;
-    if (D > 2) {
-        const double z = rt.g2d * d;
-        double e = fma(z, 1.0 / 720, 1.0 / 120);
-        e = fma(z, e, 1.0 / 24);
-        e = fma(z, e, 1.0 / 6);
-        e = fma(z, e, 0.5);
-        e = fma(z, e, 1.0);
-        e = fma(z, e, 1.0);
-        double bj = eb.y * e;                          // the table's second entry carries the factor q
-#pragma unroll
-        for (int j = 2; j < D; ++j) {
-            h[j] = h[j - 1] * bj;
-            bj *= rt.q2;
-        }
-    }
-}
-
 // Series coefficients that are not exactly representable in a 32-bit immediate live in
 // constant memory: a DFMA can take one operand straight from the constant bank, whereas a
 // literal costs two register moves every time the (register-starved) loop needs it again.
-#ifndef COEF_CONST
-#define COEF_CONST 1
-#endif
-#if COEF_CONST
-__constant__ double kInvFactC[8] = {1.0, 1.0, 0.5, 1.0 / 6, 1.0 / 24, 1.0 / 120, 1.0 / 720, 1.0 / 5040};
 __constant__ double kInvIntC[7] = {0.0, 1.0, 0.5, 1.0 / 3, 0.25, 0.2, 1.0 / 6};
-#define kInvFact(i) kInvFactC[i]
 #define kInvInt(i) kInvIntC[i]
-#else
-__host__ __device__ constexpr double inv_fact_lit(int i) { return i <= 1 ? 1.0 : inv_fact_lit(i - 1) / i; }
-#define kInvFact(i) inv_fact_lit(i)
-#define kInvInt(i) (1.0 / (i))
-#endif
+__constant__ double kInvFact3[10] = {1.0, 1.0, 0.5, 1.0 / 6, 1.0 / 24, 1.0 / 120, 1.0 / 720, 1.0 / 5040, 1.0 / 40320,
+                                     1.0 / 362880};
 
-// Branch-free twins of the two table functions for the sweep's inner loop: the table
-// index is clamped instead of tested, and the (never expected) out-of-range case is
-// reported through the return value so the caller can redo that CpG on the slow path.
-// Straight-line code lets the scheduler interleave the CpGs of one prefetch group.
-template <int D>
-__device__ __forceinline__ bool eval_basis_fast(double x, const RbfTab &rt, const double2 *__restrict__ tab,
-                                                double (&h)[D]) {
-    h[0] = 1.0;
-    if (D == 1) return false;
-    const double u = x - rt.mu1;
-    const double v = fma(u, rt.inv_s, MAGIC);
-    int idx = __double2loint(v) + rt.idx0;
-    const bool bad = (unsigned)idx >= (unsigned)rt.n_entries;
-    idx = min(max(idx, 0), rt.n_entries - 1);
-    const double u0 = (v - MAGIC) * rt.s;
-    const double d = u - u0;
-    const double2 eb = tab[idx];
-    const double w = (rt.neg_gamma * d) * fma(2.0, u0, d);
-    double c = fma(w, kInvFact(7), kInvFact(6));
-    c = fma(w, c, kInvFact(5));
-    c = fma(w, c, kInvFact(4));
-    c = fma(w, c, kInvFact(3));
-    c = fma(w, c, 0.5);
-    c = fma(w, c, 1.0);
-    c = fma(w, c, 1.0);
-    h[1] = eb.x * c;
-    if (D > 2) {
-        const double z = rt.g2d * d;
-        double e = fma(z, kInvFact(6), kInvFact(5));
-        e = fma(z, e, kInvFact(4));
-        e = fma(z, e, kInvFact(3));
-        e = fma(z, e, 0.5);
-        e = fma(z, e, 1.0);
-        e = fma(z, e, 1.0);
-        double bj = eb.y * e;                          // the table's second entry carries the factor q
+template <int N>
+__device__ __forceinline__ double exp_series(double w) {         // sum_{i <= N} w^i / i!
+    double c = fma(w, kInvFact3[N], kInvFact3[N - 1]);
 #pragma unroll
-        for (int j = 2; j < D; ++j) {
-            h[j] = h[j - 1] * bj;
-            bj *= rt.q2;
-        }
-    }
-    return bad;
+    for (int i = N - 2; i >= 2; --i) c = fma(w, c, kInvFact3[i]);
+    c = fma(w, c, 1.0);
+    return fma(w, c, 1.0);
 }
 
-__device__ __forceinline__ double trunc_mean_fast(double t, const double *__restrict__ tab, bool &bad, double &R_out) {
-    bad = !(fabs(t) < 7.99);
+// RBF row from the position x in [-1, 1], equally spaced centres mu_j = mu_1 + (j - 1) Delta:
+//   h_1 = exp(-gamma u^2),  h_{j+1} = h_j * b * q^(2j-1),  u = x - mu_1,  b = exp(2 gamma Delta u),
+//   q = exp(-gamma Delta^2).
+// The table sits on the grid x0 = j s, s a power of two (so x - x0 is exact), and holds
+// E = exp(-gamma u0^2) and B = q exp(2 gamma Delta u0); the remainder d = x - x0 enters through
+// exp(-gamma d (2 u0 + d)) and exp(2 gamma Delta d) as short series.  s is chosen by the packer
+// so that the truncation error stays below 3e-16 (rbf_table_log2 in melissa.cu).
+// Positions outside the table are reported through `bad` (the caller then uses exp()).
+template <int D>
+__device__ __forceinline__ void rbf_row3(double x, const RbfTab &rt, const double2 *__restrict__ tab,
+                                         double (&h)[D], unsigned &bad) {
+    constexpr int NW = D <= 9 ? 6 : 8;
+    h[0] = 1.0;
+    if (D == 1) return;
+    const double v = fma(x, rt.inv_s, MAGIC);
+    const int j = __double2loint(v) + rt.idx0;
+    const int jc = min(max(j, 0), rt.n_entries - 1);
+    bad |= (unsigned)(j ^ jc);
+    const double jd = v - MAGIC;
+    const double d = fma(jd, rt.neg_s, x);
+    const double2 eb = tab[jc];
+    const double w = d * fma(rt.neg_gamma, d, fma(jd, rt.cA, rt.cB));      // -gamma d (2 u0 + d)
+    h[1] = eb.x * exp_series<NW>(w);
+    if (D > 2) {
+        double bj = eb.y * exp_series<NW - 1>(rt.g2d * d);
+#pragma unroll
+        for (int q = 2; q < D; ++q) {
+            h[q] = h[q - 1] * bj;
+            if (q + 1 < D) bj *= rt.q2;
+        }
+    }
+}
+
+// E[z | z > 0], z ~ N(t, 1) = t + 1 / R(t), R = Phi / phi.  R' = 1 + t R, so the Taylor
+// coefficients about a grid point follow from the table value alone:
+//   c_0 = R0, c_1 = 1 + t0 R0, c_{n+1} = (c_{n-1} + t0 c_n) / (n + 1).
+// Spacing 1/512, order 4: indistinguishable from order 5 at 1/128 and from the erfcx closed form
+// against mpmath (tests/test_table_functions.py).  The reciprocal is MUFU.RCP64H (2^-23) plus one
+// cubically convergent step (2^-69).  |t| beyond the table is reported through `bad`.
+__device__ __forceinline__ double trunc_mean3(double t, const double *__restrict__ tab, unsigned &bad, double &R_out) {
     const double v = fma(t, (double)MILLS_SP, MAGIC);
-    const int i = min(max(__double2loint(v), -MILLS_HALF), MILLS_HALF);
+    const int i = __double2loint(v) + MILLS_HALF;
+    const int ic = min(max(i, 0), 2 * MILLS_HALF);
+    bad |= (unsigned)(i ^ ic);
     const double t0 = (v - MAGIC) * (1.0 / MILLS_SP);
     const double d = t - t0;
-    const double R0 = tab[i + MILLS_HALF];
+    const double R0 = tab[ic];
     const double c1 = fma(t0, R0, 1.0);
     const double c2 = 0.5 * fma(t0, c1, R0);
     const double c3 = fma(t0, c2, c1) * kInvInt(3);
     const double c4 = 0.25 * fma(t0, c3, c2);
-    const double c5 = fma(t0, c4, c3) * kInvInt(5);
-    double R = fma(d, c5, c4);
-    R = fma(d, R, c3);
+    double R = fma(d, c4, c3);
     R = fma(d, R, c2);
     R = fma(d, R, c1);
     R = fma(d, R, R0);
     R_out = R;
-    return t + __drcp_rn(R);
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(R));
+    const double e = fma(-R, y, 1.0);
+    y = fma(y, fma(e, e, e), y);
+    return t + y;
 }
 
 // Re-lay x / y into slices.  One thread per (slice, lane).
@@ -326,227 +249,6 @@ __device__ SLICE_SLOW_ATTR SliceSums<D> sweep_slice_slow(const double *xrow, con
         }
     }
     return o;
-}
-
-struct SweepV2Args {
-    const double *x_sell;
-    const uint32_t *ybits;
-    const int64_t *slice_xbase, *slice_ybase;
-    const int32_t *slice_len, *slice_region, *slice_cb, *lane_cell, *lane_meta, *blk_cells;
-    double *stats;
-    const double *U, *r;
-    double *log_rho, *lbbuf;
-    const double *mills_tab;
-    const double2 *rbf_tab;
-    RbfTab rt;
-    BasisDev basis;
-    int K, Tn, N;
-    unsigned long long *slice_counter;
-    int64_t S, chunk;
-};
-
-// The per-CpG sweep on slices (R/melissa_vb.R:418-435 refresh + the next iteration's
-// E-step terms :322-327 + lb_pz_qz :469-473 when WITH_LB).
-// Persistent CTAs load the two function tables once; after that every WARP is on its
-// own: it claims slices one at a time from a global counter (slices are short, ~7 us,
-// so there is no tail and no CTA barrier), keeps the E-step sums of its current cell
-// block in a private shared-memory array indexed by the cell's position in the block,
-// and adds that array to log_rho when it moves on to another block.
-template <int D, bool WITH_LB, bool UNIFORM_R>
-__global__ void __launch_bounds__(256, SWEEP_MINB) sweep_v2_kernel(SweepV2Args a) {
-    constexpr int T = D * (D + 1) / 2, R = D + T;
-    constexpr int XU = SWEEP_XU;                // CpG rows fetched per group (prefetch distance, ILP)
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int K = a.K, Tn = a.Tn;
-    const int nw = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    // shared: rbf table | mills table | per-warp U staging | per-warp accumulators
-    double2 *s_rbf = reinterpret_cast<double2 *>(smem_raw);
-    double *s_mills = reinterpret_cast<double *>(s_rbf + a.rt.n_entries);
-    double *s_u = s_mills + MILLS_N + 1;
-    double *s_acc = s_u + (SWEEP_STAGE_U ? nw * K * R : 0);
-    for (int i = threadIdx.x; i < a.rt.n_entries; i += blockDim.x) s_rbf[i] = a.rbf_tab[i];
-    for (int i = threadIdx.x; i < MILLS_N; i += blockDim.x) s_mills[i] = a.mills_tab[i];
-    for (int i = threadIdx.x; i < nw * Tn * K; i += blockDim.x) s_acc[i] = 0.0;
-    __syncthreads();
-    const double inv_K = 1.0 / (double)K;
-    double *my_u = s_u + warp * K * R;
-    double *my_acc = s_acc + warp * Tn * K;
-    double lb_local = 0.0, wrong_side = 0.0;
-    int cur_cb = -1, cur_m = -1;
-    // Slices are handed out in runs of `chunk` consecutive ones: a run stays inside one or two cell
-    // blocks, so the private sums are flushed once per run instead of once per slice (with ~3,500
-    // warps in flight, single slices would land every warp in a new block each time).
-    const int64_t chunk = a.chunk;
-    auto claim = [&]() -> int64_t {
-        unsigned long long c = 0;
-        if (lane == 0) c = atomicAdd(a.slice_counter, (unsigned long long)chunk);
-        return (int64_t)__shfl_sync(0xffffffffu, c, 0);
-    };
-    auto flush = [&]() {                        // private sums of block cur_cb -> log_rho, then clear
-        if (cur_cb < 0) return;
-        __syncwarp();
-        for (int j = lane; j < Tn; j += 32) {
-            const int cell = a.blk_cells[(int64_t)cur_cb * Tn + j];
-            for (int k = 0; k < K; ++k) {
-                const double v = my_acc[j * K + k];
-                if (cell >= 0 && v != 0.0) atomicAdd(&a.log_rho[(int64_t)cell * K + k], v);
-                my_acc[j * K + k] = 0.0;
-            }
-        }
-        __syncwarp();
-    };
-    int64_t run = claim();
-    while (run < a.S) {
-        const int64_t run_following = claim();  // claimed early: its round trip hides behind this run
-        const int64_t run_end = min(run + chunk, a.S);
-        // slice metadata is fetched one slice ahead, so that only the first slice of a run waits for it
-        int n_cb = a.slice_cb[run], n_m = a.slice_region[run], n_L = a.slice_len[run];
-        int64_t n_xb = a.slice_xbase[run], n_yb = a.slice_ybase[run];
-        int n_cell = a.lane_cell[run * 32 + lane], n_meta = a.lane_meta[run * 32 + lane];
-        for (int64_t s = run; s < run_end; ++s) {
-        const int cb = n_cb, m = n_m, L = n_L, cell = n_cell, meta = n_meta;
-        const int64_t xb = n_xb, yb = n_yb;
-        if (s + 1 < run_end) {
-            n_cb = a.slice_cb[s + 1]; n_m = a.slice_region[s + 1]; n_L = a.slice_len[s + 1];
-            n_xb = a.slice_xbase[s + 1]; n_yb = a.slice_ybase[s + 1];
-            n_cell = a.lane_cell[(s + 1) * 32 + lane]; n_meta = a.lane_meta[(s + 1) * 32 + lane];
-        }
-        if (cb != cur_cb) {
-            flush();
-            cur_cb = cb;
-        }
-        const int len = meta & 0xffff, nl = meta >> 16;
-        const bool valid = cell >= 0;
-        const double *xrow = a.x_sell + xb + lane;
-        double xa[XU];
-#pragma unroll
-        for (int u = 0; u < XU; ++u) xa[u] = xrow[u * 32];
-        uint32_t yw = a.ybits[yb + lane];
-        constexpr int RK = 8;                   // responsibilities of the lane's cell, fetched up front when K <= 8
-        double rkv[RK];
-#pragma unroll
-        for (int k = 0; k < RK; ++k)
-            rkv[k] = UNIFORM_R ? inv_K : ((valid && k < K && K <= RK) ? a.r[(int64_t)cell * K + k] : 0.0);
-        double *rec = a.stats + s * (R * 32) + (lane >> 2) * (R * 4) + (lane & 3);
-        double hh[T];
-#pragma unroll
-        for (int q = 0; q < T; ++q) hh[q] = rec[(D + q) * 4];
-        const double *um = SWEEP_STAGE_U ? my_u : a.U + (int64_t)m * K * R;
-        if (SWEEP_STAGE_U && m != cur_m) {      // consecutive slices of a run mostly share the region
-            __syncwarp();
-            for (int i = lane; i < K * R; i += 32) my_u[i] = a.U[(int64_t)m * K * R + i];
-            __syncwarp();
-            cur_m = m;
-        }
-        // -1/2 tr(H^T H (m m^T + S)) needs no E[z]: do it while the first CpG rows are in flight
-        double wbar[D];
-#pragma unroll
-        for (int d = 0; d < D; ++d) wbar[d] = 0.0;
-        auto pre_k = [&](int k, double rk) {
-            const double *u = um + k * R;
-            double trc = 0.0;
-#pragma unroll
-            for (int q = 0; q < T; ++q) trc = fma(u[D + q], hh[q], trc);
-#pragma unroll
-            for (int d = 0; d < D; ++d) wbar[d] = fma(rk, u[d], wbar[d]);
-            if (valid) {
-                my_acc[nl * K + k] += trc;                 // lanes of one slice are distinct cells
-                if (WITH_LB) lb_local = fma(rk, trc, lb_local);
-            }
-        };
-        if (K <= RK) {
-#pragma unroll
-            for (int k = 0; k < RK; ++k)
-                if (k < K) pre_k(k, rkv[k]);
-        } else {
-            for (int k = 0; k < K; ++k) pre_k(k, UNIFORM_R ? inv_K : (valid ? a.r[(int64_t)cell * K + k] : 0.0));
-        }
-        double g[D];
-#pragma unroll
-        for (int d = 0; d < D; ++d) g[d] = 0.0;
-        // Rows past a lane's own length are masked to E[z] = 0 and rows past L (read from whatever
-        // follows in x_sell, which is over-allocated by one group) are past every lane's length,
-        // so each group runs all XU rows with no trip-count test and no predicated load.
-        double lb_s = 0.0, wrong_s = 0.0;
-        bool bad_any = false;
-        const double *xp = xrow;
-        for (int i0 = 0; i0 < L; i0 += XU) {
-            double xnext[XU];
-#pragma unroll
-            for (int u = 0; u < XU; ++u) xnext[u] = xp[(XU + u) * 32];
-            xp += XU * 32;
-            uint32_t ywn = yw;
-            if (((i0 + XU) & 31) == 0 && i0 + XU < L) ywn = a.ybits[yb + (int64_t)((i0 + XU) >> 5) * 32 + lane];
-#pragma unroll
-            for (int u = 0; u < XU; ++u) {
-                const int i = i0 + u;
-                const uint32_t ybit = (yw >> (i & 31)) & 1u;
-                const uint32_t sflip = (ybit ^ 1u) << 31;             // s = +1 for y = 1, -1 for y = 0
-                const uint32_t live = i < len ? 0xffffffffu : 0u;
-                double h[D];
-                const bool bad = eval_basis_fast<D>(xa[u], a.rt, s_rbf, h);
-                double mu = wbar[0];
-#pragma unroll
-                for (int d = 1; d < D; ++d) mu = fma(h[d], wbar[d], mu);
-                const double t = __hiloint2double(__double2hiint(mu) ^ sflip, __double2loint(mu));
-                bool bad_t;
-                double Rt;
-                const double G = trunc_mean_fast(t, s_mills, bad_t, Rt);
-                bad_any |= (bad || bad_t) && live;
-                const double Ez = __hiloint2double((__double2hiint(G) ^ sflip) & live, __double2loint(G) & live);
-                g[0] += Ez;
-#pragma unroll
-                for (int d = 1; d < D; ++d) g[d] = fma(h[d], Ez, g[d]);
-                if (WITH_LB) {
-                    if (live) {
-                        // log(Phi(s mu) + 1e-10): both branches of R/melissa_vb.R:471-472 reduce to it, and
-                        // Phi = R * phi with the R the E[z] evaluation just produced (one exp + one log)
-                        lb_s += 0.5 * mu * mu + log(fma(Rt, 0.39894228040143267794 * exp(-0.5 * t * t), 1e-10));
-                        if (t < -5.0) wrong_s += 1.0;
-                    }
-                }
-            }
-#pragma unroll
-            for (int u = 0; u < XU; ++u) xa[u] = xnext[u];
-            yw = ywn;
-        }
-        if (__any_sync(0xffffffffu, bad_any)) {                    // never taken on sane data
-            WBar<D> wb;
-#pragma unroll
-            for (int d = 0; d < D; ++d) wb.w[d] = wbar[d];
-            const SliceSums<D> o = sweep_slice_slow<D, WITH_LB>(xrow, a.ybits + yb + lane, L, len, wb, &a.basis);
-#pragma unroll
-            for (int d = 0; d < D; ++d) g[d] = o.g[d];
-            lb_s = o.lb;
-            wrong_s = o.wrong;
-        }
-        if (WITH_LB) {
-            lb_local += lb_s;
-            wrong_side += wrong_s;
-        }
-#pragma unroll
-        for (int d = 0; d < D; ++d) rec[d * 4] = g[d];
-        if (valid) {
-            for (int k = 0; k < K; ++k) {
-                const double *u = um + k * R;
-                double lin = 0.0;
-#pragma unroll
-                for (int d = 0; d < D; ++d) lin = fma(u[d], g[d], lin);
-                my_acc[nl * K + k] += lin;
-            }
-        }
-        }
-        run = run_following;
-    }
-    flush();
-    if (WITH_LB) {
-        lb_local = warp_sum(lb_local);
-        wrong_side = warp_sum(wrong_side);
-        if (lane == 0) {
-            atomicAdd(&a.lbbuf[0], lb_local);
-            if (wrong_side != 0.0) atomicAdd(&a.lbbuf[1], wrong_side);
-        }
-    }
 }
 
 // Contraction on slices: acc[m,k,j] = sum over the region's slices and lanes of
@@ -745,12 +447,18 @@ mle_kernel(const double *__restrict__ x_sell, const uint32_t *__restrict__ ybits
                 if ((i & 31) == 0) yw = yrow[(int64_t)(i >> 5) * 32];
                 const bool yi = (yw >> (i & 31)) & 1u;
                 double h[D];
-                eval_basis_tab<D>(xrow[(int64_t)i * 32], rt, s_rbf, basis, h);
+                unsigned bad = 0;
+                const double xi = xrow[(int64_t)i * 32];
+                rbf_row3<D>(xi, rt, s_rbf, h, bad);
+                if (bad) eval_basis<D>(xi, basis, h);                // position outside the table
                 double eta = w[0];
 #pragma unroll
                 for (int d = 1; d < D; ++d) eta = fma(h[d], w[d], eta);
                 const double t = yi ? eta : -eta;
-                const double G = trunc_mean_tab(t, s_mills);     // t + phi/Phi
+                double Rt;
+                bad = 0;
+                double G = trunc_mean3(t, s_mills, bad, Rt);     // t + phi/Phi
+                if (bad) G = trunc_mean(t);                      // |t| beyond the table
                 double lam = G - t;                              // phi(t) / Phi(t)
                 double hess = lam * G;                           // -(d^2/d eta^2) log Phi(s eta)
                 if (i >= len) { lam = 0.0; hess = 0.0; }

@@ -1,0 +1,261 @@
+// The per-CpG sweep, third generation (R/melissa_vb.R:418-435 refresh + the next iteration's
+// E-step terms :322-327 + lb_pz_qz :469-473 when WITH_LB).
+//
+// What changed against sweep_v2 (round 1) and why:
+//   * ONE persistent CTA per SM.  The two function tables are therefore paid once per SM and can
+//     be finer (truncated-normal table at spacing 1/512 with a 4th-order series, RBF table at a
+//     power-of-two spacing with 6th/5th-order series): 53 FP64 operations per CpG instead of 74.
+//   * The E-step sums of a cell block live in ONE CTA-wide shared array, not one per warp, so
+//     the cell block (= the pool the slices of a region are sorted in) no longer shrinks with K:
+//     256 cells at every K, which takes the row padding at K = 10 from 1.39x to 1.07x.
+//   * The CTA claims CHUNKS (runs of slices inside one cell block) from a global counter, its
+//     warps claim slices of the chunk from a shared counter; the block's sums are flushed to
+//     global memory once per chunk.
+//   * Those sums are accumulated in 128-bit fixed point (integer atomics, fx128.cuh), so the
+//     result does not depend on the order in which warps and CTAs arrive: log rho, and with it
+//     the hard labels (first arg-max, R/melissa_vb.R:212-213), are reproducible bit for bit.
+//
+// Included from melissa.cu inside its anonymous namespace, after sliced.cuh.
+#pragma once
+
+struct Sweep3Args {
+    const double *x_sell;
+    const uint32_t *ybits;
+    const int64_t *slice_xbase, *slice_ybase;
+    const int32_t *slice_len, *slice_region, *slice_cb, *lane_cell, *lane_meta, *blk_cells;
+    const int32_t *chunk_ptr;                 // [NC + 1] first slice of every chunk; a chunk stays inside one cell block
+    double *stats;
+    const double *U, *r;
+    unsigned long long *log_rho_fx;           // [N][K][2]
+    unsigned long long *lb_fx;                // [4]: lb_pz_qz (lo, hi), #CpG with s mu < -5, unused
+    unsigned int *poison;                     // set when a term is non-finite or beyond the fixed-point range
+    const double *mills_tab;
+    const double2 *rbf_tab;
+    RbfTab rt;
+    BasisDev basis;
+    int K, Tn, NC, G;
+    unsigned int *chunk_counter;
+};
+
+#ifndef SWEEP3_XU
+#define SWEEP3_XU 2
+#endif
+
+template <int D, bool WITH_LB>
+__global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a) {
+    constexpr int T = D * (D + 1) / 2, R = D + T;
+    constexpr int XU = SWEEP3_XU;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int K = a.K, Tn = a.Tn;
+    const int nw = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int UR = (K * R + 1) & ~1;
+    // shared: rbf table | mills table | block sums (fixed point) | per-warp U[m] | lb sums | control words
+    double2 *s_rbf = reinterpret_cast<double2 *>(smem_raw);
+    double *s_mills = reinterpret_cast<double *>(s_rbf + a.rt.n_entries);
+    unsigned long long *s_acc = reinterpret_cast<unsigned long long *>(s_mills + MILLS_N + 1);
+    double *s_u = reinterpret_cast<double *>(s_acc + 2 * (size_t)Tn * K);
+    unsigned long long *s_lb = reinterpret_cast<unsigned long long *>(s_u + (size_t)nw * UR);    // [2] + wrong-side count
+    int *s_ctl = reinterpret_cast<int *>(s_lb + 4);                                             // cursor, next chunk
+    for (int i = threadIdx.x; i < a.rt.n_entries; i += blockDim.x) s_rbf[i] = a.rbf_tab[i];
+    for (int i = threadIdx.x; i < MILLS_N; i += blockDim.x) s_mills[i] = a.mills_tab[i];
+    for (int i = threadIdx.x; i < 2 * Tn * K; i += blockDim.x) s_acc[i] = 0ull;
+    if (threadIdx.x < 4) s_lb[threadIdx.x] = 0ull;
+    if (threadIdx.x == 0) s_ctl[1] = (int)atomicAdd(a.chunk_counter, 1u);
+    __syncthreads();
+    double *my_u = s_u + (size_t)warp * UR;
+    int cur_m = -1;
+    int chunk = s_ctl[1];
+    const int G = a.G;
+    while (chunk < a.NC) {
+        const int c_beg = a.chunk_ptr[chunk], c_end = a.chunk_ptr[chunk + 1];
+        const int cb = a.slice_cb[c_beg];
+        __syncthreads();                                   // everybody has read s_ctl[1]; the last flush is done
+        if (threadIdx.x == 0) {
+            s_ctl[0] = c_beg;
+            s_ctl[1] = (int)atomicAdd(a.chunk_counter, 1u);        // the chunk after this one, claimed early
+        }
+        __syncthreads();
+        auto claim = [&]() -> int {
+            int c = 0;
+            if (lane == 0) c = atomicAdd(&s_ctl[0], G);
+            return __shfl_sync(0xffffffffu, c, 0);
+        };
+        int run = claim();
+        // slice metadata is fetched one slice ahead
+        int n_m = 0, n_L = 0, n_cell = -1, n_meta = 0;
+        int64_t n_xb = 0, n_yb = 0;
+        auto fetch_meta = [&](int s) {
+            n_m = a.slice_region[s]; n_L = a.slice_len[s];
+            n_xb = a.slice_xbase[s]; n_yb = a.slice_ybase[s];
+            n_cell = a.lane_cell[(int64_t)s * 32 + lane]; n_meta = a.lane_meta[(int64_t)s * 32 + lane];
+        };
+        if (run < c_end) fetch_meta(run);
+        while (run < c_end) {
+            const int run_following = claim();
+            const int run_end = min(run + G, c_end);
+            for (int s = run; s < run_end; ++s) {
+                const int m = n_m, L = n_L, cell = n_cell, meta = n_meta;
+                const int64_t xb = n_xb, yb = n_yb;
+                {
+                    const int s_next = s + 1 < run_end ? s + 1 : run_following;
+                    if (s_next < c_end) fetch_meta(s_next);
+                }
+                const int len = meta & 0xffff, nl = meta >> 16;
+                const bool valid = cell >= 0;
+                const double *xrow = a.x_sell + xb + lane;
+                double xa[XU];
+#pragma unroll
+                for (int u = 0; u < XU; ++u) xa[u] = xrow[u * 32];
+                uint32_t yw = a.ybits[yb + lane];
+                if (m != cur_m) {                           // consecutive slices of a run mostly share the region
+                    __syncwarp();
+                    const double *src = a.U + (int64_t)m * K * R;
+                    for (int i = lane; i < K * R; i += 32) my_u[i] = src[i];
+                    __syncwarp();
+                    cur_m = m;
+                }
+                const double *rp = a.r + (int64_t)(valid ? cell : 0) * K;
+                double wbar[D];
+#pragma unroll
+                for (int d = 0; d < D; ++d) wbar[d] = 0.0;
+#pragma unroll 2
+                for (int k = 0; k < K; ++k) {
+                    const double rk = valid ? rp[k] : 0.0;
+                    const double *u = my_u + k * R;
+#pragma unroll
+                    for (int d = 0; d < D; ++d) wbar[d] = fma(rk, u[d], wbar[d]);
+                }
+                double g[D];
+#pragma unroll
+                for (int d = 0; d < D; ++d) g[d] = 0.0;
+                // Rows past a lane's own length contribute nothing (predicated), rows past L (read from
+                // whatever follows in x_sell, which is over-allocated by two groups) are past every lane's
+                // length, so each group runs all XU rows with no trip-count test and no predicated load.
+                double lb_s = 0.0;
+                int wrong_s = 0;
+                unsigned bad = 0;
+                const double *xp = xrow;
+                for (int i0 = 0; i0 < L; i0 += XU) {
+                    double xnext[XU];
+#pragma unroll
+                    for (int u = 0; u < XU; ++u) xnext[u] = xp[(XU + u) * 32];
+                    xp += XU * 32;
+                    uint32_t ywn = yw;
+                    if (((i0 + XU) & 31) == 0 && i0 + XU < L) ywn = a.ybits[yb + (int64_t)((i0 + XU) >> 5) * 32 + lane];
+#pragma unroll
+                    for (int u = 0; u < XU; ++u) {
+                        const int i = i0 + u;
+                        const uint32_t sflip = (((yw >> (i & 31)) & 1u) ^ 1u) << 31;      // s = +1 for y = 1, -1 for y = 0
+                        double h[D];
+                        unsigned bad_row = 0;
+                        rbf_row3<D>(xa[u], a.rt, s_rbf, h, bad_row);
+                        double mu = wbar[0];
+#pragma unroll
+                        for (int d = 1; d < D; ++d) mu = fma(h[d], wbar[d], mu);
+                        const double t = __hiloint2double(__double2hiint(mu) ^ sflip, __double2loint(mu));
+                        double Rt;
+                        const double Gt = trunc_mean3(t, s_mills, bad_row, Rt);
+                        const double Ez = __hiloint2double(__double2hiint(Gt) ^ sflip, __double2loint(Gt));
+                        if (i < len) {
+                            bad |= bad_row;
+                            g[0] += Ez;
+#pragma unroll
+                            for (int d = 1; d < D; ++d) g[d] = fma(h[d], Ez, g[d]);
+                            if (WITH_LB) {
+                                // log(Phi(s mu) + 1e-10): both branches of R/melissa_vb.R:471-472 reduce to it, and
+                                // Phi = R * phi with the R the E[z] evaluation just produced (one exp + one log)
+                                lb_s += fma(0.5 * mu, mu, log(fma(Rt, 0.39894228040143267794 * exp(-0.5 * t * t), 1e-10)));
+                                wrong_s += t < -5.0;
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < XU; ++u) xa[u] = xnext[u];
+                    yw = ywn;
+                }
+                if (__any_sync(0xffffffffu, bad != 0)) {                   // never taken on sane data
+                    WBar<D> wb;
+#pragma unroll
+                    for (int d = 0; d < D; ++d) wb.w[d] = wbar[d];
+                    const SliceSums<D> o = sweep_slice_slow<D, WITH_LB>(xrow, a.ybits + yb + lane, L, len, wb, &a.basis);
+#pragma unroll
+                    for (int d = 0; d < D; ++d) g[d] = o.g[d];
+                    lb_s = o.lb;
+                    wrong_s = (int)o.wrong;
+                }
+                double *rec = a.stats + (int64_t)s * (R * 32) + (lane >> 2) * (R * 4) + (lane & 3);
+#pragma unroll
+                for (int d = 0; d < D; ++d) rec[d * 4] = g[d];
+                // E-step terms of the next iteration (R/melissa_vb.R:325-326): U[m,k] . [g | H^T H]
+                double hh[T];
+#pragma unroll
+                for (int q = 0; q < T; ++q) hh[q] = rec[(D + q) * 4];
+                if (valid) {
+                    unsigned long long *acc = s_acc + 2 * (size_t)nl;
+                    bool over = false;
+                    for (int k = 0; k < K; ++k) {
+                        const double *u = my_u + k * R;
+                        double trc = 0.0, lin = 0.0;
+#pragma unroll
+                        for (int q = 0; q < T; ++q) trc = fma(u[D + q], hh[q], trc);
+#pragma unroll
+                        for (int d = 0; d < D; ++d) lin = fma(u[d], g[d], lin);
+                        const double v = lin + trc;
+                        over |= !(fabs(v) < FX_LIMIT);
+                        fx_add(acc + 2 * (size_t)k * Tn, fx_from_double(v));
+                        if (WITH_LB) lb_s = fma(rp[k], trc, lb_s);
+                    }
+                    if (over) atomicOr(a.poison, 1u);
+                }
+                if (WITH_LB) {
+                    // per-slice sums go through the fixed butterfly and then into the fixed-point
+                    // accumulator, so the bound does not depend on which warp took which slice either
+                    if (!valid) lb_s = 0.0;
+                    lb_s = warp_sum(lb_s);
+                    wrong_s = __reduce_add_sync(0xffffffffu, wrong_s);
+                    if (lane == 0) {
+                        if (!(fabs(lb_s) < FX_LIMIT)) atomicOr(a.poison, 1u);
+                        fx_add(s_lb, fx_from_double(lb_s));
+                        if (wrong_s) atomicAdd(s_lb + 2, (unsigned long long)wrong_s);
+                    }
+                }
+            }
+            run = run_following;
+        }
+        __syncthreads();
+        const int chunk_next = s_ctl[1];
+        // the block's sums -> global, then clear
+        for (int idx = threadIdx.x; idx < Tn * K; idx += blockDim.x) {
+            const int k = idx / Tn, j = idx - k * Tn;
+            const unsigned long long lo = s_acc[2 * idx], hi = s_acc[2 * idx + 1];
+            if (lo | hi) {
+                const int cell = a.blk_cells[(int64_t)cb * Tn + j];
+                Fx128 f;
+                f.lo = lo;
+                f.hi = (long long)hi;
+                fx_add(a.log_rho_fx + 2 * ((int64_t)cell * K + k), f);
+                s_acc[2 * idx] = 0ull;
+                s_acc[2 * idx + 1] = 0ull;
+            }
+        }
+        chunk = chunk_next;
+    }
+    if (WITH_LB) {
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            Fx128 f;
+            f.lo = s_lb[0];
+            f.hi = (long long)s_lb[1];
+            if (f.lo | (unsigned long long)f.hi) fx_add(a.lb_fx, f);
+            if (s_lb[2]) atomicAdd(a.lb_fx + 2, s_lb[2]);
+        }
+    }
+}
+
+// lb_fx -> lbbuf (doubles, the all-reduce payload of bound iterations), then clear.
+__global__ void lb_finish_kernel(unsigned long long *lb_fx, double *lbbuf) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    lbbuf[0] = fx_to_double(lb_fx[0], lb_fx[1]);
+    lbbuf[1] = (double)lb_fx[2];
+    lb_fx[0] = lb_fx[1] = lb_fx[2] = lb_fx[3] = 0ull;
+}

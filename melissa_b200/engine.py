@@ -172,6 +172,15 @@ class Engine:
     def launch_count(self) -> int:
         return int(self.lib.melissa_launch_count(self.h))
 
+    def layout_info(self) -> dict:
+        """Shape of the packed layout (melissa_layout_info)."""
+        v = (C.c_int64 * 8)()
+        _lib.check(self.lib.melissa_layout_info(self.h, v, 8))
+        keys = ("sliced", "cell_block", "slices", "cpg_slots", "cpgs", "pairs", "chunks", "sweep_warps")
+        out = dict(zip(keys, (int(x) for x in v)))
+        out["row_padding"] = out["cpg_slots"] / max(1, out["cpgs"])
+        return out
+
     KERNELS = dict(sweep=0, resp=1, contract=2, solve=3, scalars=4, lb=5)
 
     def profile(self, on: bool):
