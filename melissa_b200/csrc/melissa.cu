@@ -1085,13 +1085,14 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
 #undef PUT
     }
     // + 2 prefetch groups of slack: the sweep reads one group past the end of every slice
-    if ((rc = dev_alloc(&sl->x_sell, sl->x_len + 2 * SWEEP3_XU * 32)) || (rc = dev_alloc(&sl->ybits, sl->y_len)) ||
+    // slack: the sweep's x ring reads up to NST groups past the end of a slice
+    if ((rc = dev_alloc(&sl->x_sell, sl->x_len + 2 * SWEEP3_NST * SWEEP3_XU * 32)) || (rc = dev_alloc(&sl->ybits, sl->y_len)) ||
         (rc = dev_alloc(&sl->stats, S * h->R * 32)) || (rc = dev_alloc(&sl->mills_tab, MILLS_N)) ||
         (rc = dev_alloc(&sl->chunk_counter, 1))) {
         cudaFree(d_src);
         return rc;
     }
-    cudaMemsetAsync(sl->x_sell + sl->x_len, 0, (size_t)2 * SWEEP3_XU * 32 * sizeof(double), nullptr);
+    cudaMemsetAsync(sl->x_sell + sl->x_len, 0, (size_t)2 * SWEEP3_NST * SWEEP3_XU * 32 * sizeof(double), nullptr);
     tm.lap("upload index arrays");
     const int grid = (int)((S * 32 + 255) / 256);
     sell_fill_kernel<<<grid, 256>>>(h->x, h->y, d_src, sl->lane_meta, sl->slice_xbase, sl->slice_ybase, sl->slice_len,
@@ -1120,7 +1121,8 @@ size_t sweep3_smem(const melissa_handle *h, int nw) {
     const Sliced *sl = h->sl;
     const size_t UR = ((size_t)h->K * h->R + 1) & ~(size_t)1;
     return (size_t)sl->rt.n_entries * sizeof(double2) + ((size_t)MILLS_N + 1) * sizeof(double) +
-           2 * (size_t)sl->Tn * h->K * sizeof(unsigned long long) + (size_t)nw * UR * sizeof(double) + 4 * 8 + 16;
+           2 * (size_t)sl->Tn * h->K * sizeof(unsigned long long) + (size_t)nw * UR * sizeof(double) +
+           (size_t)nw * SWEEP3_NST * SWEEP3_XU * 32 * sizeof(double) + 4 * 8 + 16;
 }
 
 // Most warps (of SWEEP3_THREADS / 32) whose staging areas still fit next to the rest; 0 = not even four.

@@ -38,13 +38,27 @@ struct Sweep3Args {
 };
 
 #ifndef SWEEP3_XU
-#define SWEEP3_XU 2
+#define SWEEP3_XU 2           // CpG rows per group: one 16-byte cp.async per lane moves a group (2 rows x 256 bytes)
 #endif
+#ifndef SWEEP3_NST
+#define SWEEP3_NST 4          // groups of the x ring per warp: NST - 1 groups (6 rows) are in flight ahead of the arithmetic
+#endif
+static_assert(SWEEP3_XU == 2, "the x ring moves two rows per cp.async");
+static_assert((SWEEP3_NST & (SWEEP3_NST - 1)) == 0, "ring size must be a power of two");
+
+// One group of x (rows 2g, 2g + 1 of a slice: 512 contiguous bytes) global -> shared, no registers
+// involved: lanes 0-15 move the first row, lanes 16-31 the second, 16 bytes each, bypassing L1.
+__device__ __forceinline__ void x_group_async(uint32_t dst_smem, const double *src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_smem), "l"(src) : "memory");
+}
+__device__ __forceinline__ void x_group_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void x_group_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 template <int D, bool WITH_LB>
 __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a) {
     constexpr int T = D * (D + 1) / 2, R = D + T;
-    constexpr int XU = SWEEP3_XU;
+    constexpr int XU = SWEEP3_XU, NST = SWEEP3_NST;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int K = a.K, Tn = a.Tn;
     const int nw = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -54,7 +68,8 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
     double *s_mills = reinterpret_cast<double *>(s_rbf + a.rt.n_entries);
     unsigned long long *s_acc = reinterpret_cast<unsigned long long *>(s_mills + MILLS_N + 1);
     double *s_u = reinterpret_cast<double *>(s_acc + 2 * (size_t)Tn * K);
-    unsigned long long *s_lb = reinterpret_cast<unsigned long long *>(s_u + (size_t)nw * UR);    // [2] + wrong-side count
+    double *s_x = s_u + (size_t)nw * UR;                                                         // per-warp ring of x groups
+    unsigned long long *s_lb = reinterpret_cast<unsigned long long *>(s_x + (size_t)nw * NST * XU * 32);   // [2] + wrong-side count
     int *s_ctl = reinterpret_cast<int *>(s_lb + 4);                                             // cursor, next chunk
     for (int i = threadIdx.x; i < a.rt.n_entries; i += blockDim.x) s_rbf[i] = a.rbf_tab[i];
     for (int i = threadIdx.x; i < MILLS_N; i += blockDim.x) s_mills[i] = a.mills_tab[i];
@@ -63,6 +78,16 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
     if (threadIdx.x == 0) s_ctl[1] = (int)atomicAdd(a.chunk_counter, 1u);
     __syncthreads();
     double *my_u = s_u + (size_t)warp * UR;
+    // x ring of this warp.  Groups are issued and consumed strictly in order: `iss` / `con` count them,
+    // slot = counter mod NST.  Between slices NST - 1 groups stay in flight (`pre` of them belong to the
+    // slice that comes next), so that a slice does not start with an empty pipeline.
+    // (NST - 1 groups are always between the issue and the consume position, so one slot offset serves both.)
+    constexpr uint32_t SLOT_BYTES = XU * 256, RING_MASK = (NST - 1) * SLOT_BYTES;
+    const uint32_t my_x_smem = (uint32_t)__cvta_generic_to_shared(s_x + (size_t)warp * NST * XU * 32);
+    const uint32_t my_x_fill = my_x_smem + (uint32_t)lane * 16;      // this lane's 16 bytes of a group
+    const uint32_t my_x_read = my_x_smem + (uint32_t)lane * 8;       // this lane's CpG of a row
+    uint32_t slot = 0;                                               // byte offset of the next slot to fill
+    int pre = 0;
     int cur_m = -1;
     int chunk = s_ctl[1];
     const int G = a.G;
@@ -96,16 +121,27 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
             for (int s = run; s < run_end; ++s) {
                 const int m = n_m, L = n_L, cell = n_cell, meta = n_meta;
                 const int64_t xb = n_xb, yb = n_yb;
+                bool has_next;
                 {
                     const int s_next = s + 1 < run_end ? s + 1 : run_following;
-                    if (s_next < c_end) fetch_meta(s_next);
+                    has_next = s_next < c_end;
+                    if (has_next) fetch_meta(s_next);
                 }
                 const int len = meta & 0xffff, nl = meta >> 16;
                 const bool valid = cell >= 0;
                 const double *xrow = a.x_sell + xb + lane;
-                double xa[XU];
+                const double *xgrp = a.x_sell + xb + 2 * lane;              // + 64 g: this lane's 16 bytes of group g
+                const int ng = (L + XU - 1) / XU;
+                const double *fsrc = xgrp + 64 * (NST - 1);                 // next group to fetch
+                if (pre != NST - 1) {                                       // cold start: nothing usable in flight
+                    x_group_wait<0>();
 #pragma unroll
-                for (int u = 0; u < XU; ++u) xa[u] = xrow[u * 32];
+                    for (int gq = 0; gq < NST - 1; ++gq) {                 // (groups past the slice read the slack / the next slice: harmless)
+                        x_group_async(my_x_fill + slot, xgrp + 64 * gq);
+                        x_group_commit();
+                        slot = (slot + SLOT_BYTES) & RING_MASK;
+                    }
+                }
                 uint32_t yw = a.ybits[yb + lane];
                 if (m != cur_m) {                           // consecutive slices of a run mostly share the region
                     __syncwarp();
@@ -134,12 +170,22 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
                 double lb_s = 0.0;
                 int wrong_s = 0;
                 unsigned bad = 0;
-                const double *xp = xrow;
+                // the slice after this one is prefetched into the ring while this one's last groups are consumed
+                // (n_* already hold its metadata); short slices skip that and start cold
+                const bool chain = has_next && ng >= NST - 1;
+                const int i_switch = chain ? XU * (ng - (NST - 1)) : 0x7fffffff;   // from this row on, fetch the next slice
                 for (int i0 = 0; i0 < L; i0 += XU) {
-                    double xnext[XU];
+                    if (i0 == i_switch) fsrc = a.x_sell + n_xb + 2 * lane;
+                    x_group_async(my_x_fill + slot, fsrc);
+                    x_group_commit();
+                    fsrc += 64;
+                    slot = (slot + SLOT_BYTES) & RING_MASK;                 // = the slot NST - 1 groups back: the one to consume
+                    x_group_wait<NST - 1>();
+                    __syncwarp();
+                    double xa[XU];
 #pragma unroll
-                    for (int u = 0; u < XU; ++u) xnext[u] = xp[(XU + u) * 32];
-                    xp += XU * 32;
+                    for (int u = 0; u < XU; ++u)
+                        asm volatile("ld.shared.f64 %0, [%1];" : "=d"(xa[u]) : "r"(my_x_read + slot + u * 256) : "memory");
                     uint32_t ywn = yw;
                     if (((i0 + XU) & 31) == 0 && i0 + XU < L) ywn = a.ybits[yb + (int64_t)((i0 + XU) >> 5) * 32 + lane];
 #pragma unroll
@@ -169,10 +215,9 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
                             }
                         }
                     }
-#pragma unroll
-                    for (int u = 0; u < XU; ++u) xa[u] = xnext[u];
                     yw = ywn;
                 }
+                pre = chain ? NST - 1 : 0;
                 if (__any_sync(0xffffffffu, bad != 0)) {                   // never taken on sane data
                     WBar<D> wb;
 #pragma unroll
