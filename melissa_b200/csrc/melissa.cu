@@ -1029,8 +1029,10 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
     // ---- chunks of the sweep: runs of consecutive slices that stay inside one cell block
     std::vector<int32_t> chunk_ptr;
     {
-        const int64_t target = g_opt_sweep_chunk > 0 ? g_opt_sweep_chunk
-                                                     : std::max<int64_t>(48, std::min<int64_t>(2048, S / ((int64_t)h->sm_count * 16)));
+        // (a chunk adds to a shared accumulator at most once per slice; LIMB_MAX_ADDS is what its limbs can absorb)
+        const int64_t target = std::min<int64_t>(LIMB_MAX_ADDS, g_opt_sweep_chunk > 0
+                                   ? g_opt_sweep_chunk
+                                   : std::max<int64_t>(384, std::min<int64_t>(2048, S / ((int64_t)h->sm_count * 16))));
         int64_t s0 = 0;
         for (int t = 0; t < nthr; ++t) {
             const auto &cbv = parts[(size_t)t].slice_cb;
@@ -1121,7 +1123,7 @@ size_t sweep3_smem(const melissa_handle *h, int nw) {
     const Sliced *sl = h->sl;
     const size_t UR = ((size_t)h->K * h->R + 1) & ~(size_t)1;
     return (size_t)sl->rt.n_entries * sizeof(double2) + ((size_t)MILLS_N + 1) * sizeof(double) +
-           2 * (size_t)sl->Tn * h->K * sizeof(unsigned long long) + (size_t)nw * UR * sizeof(double) +
+           4 * (size_t)sl->Tn * h->K * sizeof(unsigned int) + (size_t)nw * UR * sizeof(double) +
            (size_t)nw * SWEEP3_NST * SWEEP3_XU * 32 * sizeof(double) + 4 * 8 + 16;
 }
 

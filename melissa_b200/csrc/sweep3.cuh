@@ -66,14 +66,14 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
     // shared: rbf table | mills table | block sums (fixed point) | per-warp U[m] | lb sums | control words
     double2 *s_rbf = reinterpret_cast<double2 *>(smem_raw);
     double *s_mills = reinterpret_cast<double *>(s_rbf + a.rt.n_entries);
-    unsigned long long *s_acc = reinterpret_cast<unsigned long long *>(s_mills + MILLS_N + 1);
-    double *s_u = reinterpret_cast<double *>(s_acc + 2 * (size_t)Tn * K);
+    unsigned int *s_acc = reinterpret_cast<unsigned int *>(s_mills + MILLS_N + 1);      // [4 limbs][K][Tn]
+    double *s_u = reinterpret_cast<double *>(s_acc + 4 * (size_t)Tn * K);
     double *s_x = s_u + (size_t)nw * UR;                                                         // per-warp ring of x groups
     unsigned long long *s_lb = reinterpret_cast<unsigned long long *>(s_x + (size_t)nw * NST * XU * 32);   // [2] + wrong-side count
     int *s_ctl = reinterpret_cast<int *>(s_lb + 4);                                             // cursor, next chunk
     for (int i = threadIdx.x; i < a.rt.n_entries; i += blockDim.x) s_rbf[i] = a.rbf_tab[i];
     for (int i = threadIdx.x; i < MILLS_N; i += blockDim.x) s_mills[i] = a.mills_tab[i];
-    for (int i = threadIdx.x; i < 2 * Tn * K; i += blockDim.x) s_acc[i] = 0ull;
+    for (int i = threadIdx.x; i < 4 * Tn * K; i += blockDim.x) s_acc[i] = 0u;
     if (threadIdx.x < 4) s_lb[threadIdx.x] = 0ull;
     if (threadIdx.x == 0) s_ctl[1] = (int)atomicAdd(a.chunk_counter, 1u);
     __syncthreads();
@@ -236,7 +236,7 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
 #pragma unroll
                 for (int q = 0; q < T; ++q) hh[q] = rec[(D + q) * 4];
                 if (valid) {
-                    unsigned long long *acc = s_acc + 2 * (size_t)nl;
+                    unsigned int *acc = s_acc + nl;
                     bool over = false;
                     for (int k = 0; k < K; ++k) {
                         const double *u = my_u + k * R;
@@ -246,8 +246,8 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
 #pragma unroll
                         for (int d = 0; d < D; ++d) lin = fma(u[d], g[d], lin);
                         const double v = lin + trc;
-                        over |= !(fabs(v) < FX_LIMIT);
-                        fx_add(acc + 2 * (size_t)k * Tn, fx_from_double(v));
+                        over |= !(fabs(v) < LIMB_LIMIT);
+                        limb_add_shared(acc + k * Tn, K * Tn, v);
                         if (WITH_LB) lb_s = fma(rp[k], trc, lb_s);
                     }
                     if (over) atomicOr(a.poison, 1u);
@@ -270,17 +270,17 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
         __syncthreads();
         const int chunk_next = s_ctl[1];
         // the block's sums -> global, then clear
-        for (int idx = threadIdx.x; idx < Tn * K; idx += blockDim.x) {
+        const int KT = K * Tn;
+        for (int idx = threadIdx.x; idx < KT; idx += blockDim.x) {
             const int k = idx / Tn, j = idx - k * Tn;
-            const unsigned long long lo = s_acc[2 * idx], hi = s_acc[2 * idx + 1];
-            if (lo | hi) {
+            const unsigned int l0 = s_acc[idx], l1 = s_acc[KT + idx], l2 = s_acc[2 * KT + idx], l3 = s_acc[3 * KT + idx];
+            if (l0 | l1 | l2 | l3) {
                 const int cell = a.blk_cells[(int64_t)cb * Tn + j];
-                Fx128 f;
-                f.lo = lo;
-                f.hi = (long long)hi;
-                fx_add(a.log_rho_fx + 2 * ((int64_t)cell * K + k), f);
-                s_acc[2 * idx] = 0ull;
-                s_acc[2 * idx + 1] = 0ull;
+                fx_add(a.log_rho_fx + 2 * ((int64_t)cell * K + k), limb_to_fx(l0, l1, l2, l3));
+                s_acc[idx] = 0u;
+                s_acc[KT + idx] = 0u;
+                s_acc[2 * KT + idx] = 0u;
+                s_acc[3 * KT + idx] = 0u;
             }
         }
         chunk = chunk_next;
