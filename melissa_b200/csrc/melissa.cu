@@ -1140,6 +1140,140 @@ __global__ void fill_kernel(double *p, int64_t n, double v) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
 }
 
+// ---- development check ("debug_estep" option): the E-step sums of the last sweep recomputed pair by pair from
+//      the stored records and compared, accumulator by accumulator, with what the sweep left in log_rho_fx
+template <int D>
+__global__ void estep_check_kernel(const double *__restrict__ stats, const int32_t *__restrict__ slice_region,
+                                   const int32_t *__restrict__ lane_cell, const double *__restrict__ U,
+                                   unsigned long long *__restrict__ dbg, int64_t n_lanes, int K) {
+    constexpr int T = D * (D + 1) / 2, R = D + T;
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_lanes) return;
+    const int cell = lane_cell[t];
+    if (cell < 0) return;
+    const int64_t s = t >> 5;
+    const int lane = (int)(t & 31), m = slice_region[s];
+    const double *rec = stats + s * (R * 32) + (lane >> 2) * (R * 4) + (lane & 3);
+    for (int k = 0; k < K; ++k) {
+        const double *u = U + ((int64_t)m * K + k) * R;
+        double trc = 0.0, lin = 0.0;
+        for (int q = 0; q < T; ++q) trc = fma(u[D + q], rec[(D + q) * 4], trc);
+        for (int d = 0; d < D; ++d) lin = fma(u[d], rec[d * 4], lin);
+        const double v = lin + trc;
+        // same 2^-44 image as the sweep's limbs
+        const double f = floor(v * 0x1p44);
+        const long long hi = (long long)floor(f * 0x1p-44);
+        Fx128 fx;
+        fx.hi = hi;
+        fx.lo = (unsigned long long)(f - (double)hi * 0x1p44) << 20;
+        fx_add(dbg + 2 * ((int64_t)cell * K + k), fx);
+    }
+}
+// the same check for g = H^T E[z]: recomputed per lane with exp / erfcx from x, r and U
+template <int D>
+__global__ void g_check_kernel(const double *__restrict__ x_sell, const uint32_t *__restrict__ ybits,
+                               const int64_t *__restrict__ slice_xbase, const int64_t *__restrict__ slice_ybase,
+                               const int32_t *__restrict__ slice_len, const int32_t *__restrict__ lane_meta,
+                               const double *__restrict__ stats, const int32_t *__restrict__ slice_region,
+                               const int32_t *__restrict__ lane_cell, const double *__restrict__ U, const double *__restrict__ r,
+                               unsigned long long *__restrict__ out, int64_t n_lanes, int K, BasisDev basis) {
+    constexpr int T = D * (D + 1) / 2, R = D + T;
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_lanes) return;
+    const int cell = lane_cell[t];
+    if (cell < 0) return;
+    const int64_t s = t >> 5;
+    const int lane = (int)(t & 31), m = slice_region[s];
+    const double *rec = stats + s * (R * 32) + (lane >> 2) * (R * 4) + (lane & 3);
+    WBar<D> wb;
+    for (int d = 0; d < D; ++d) wb.w[d] = 0.0;
+    for (int k = 0; k < K; ++k)
+        for (int d = 0; d < D; ++d) wb.w[d] = fma(r[(int64_t)cell * K + k], U[((int64_t)m * K + k) * R + d], wb.w[d]);
+    const SliceSums<D> o = sweep_slice_slow<D, false>(x_sell + slice_xbase[s] + lane, ybits + slice_ybase[s] + lane, slice_len[s],
+                                                      lane_meta[t] & 0xffff, wb, &basis);
+    for (int d = 0; d < D; ++d) {
+        const double got = rec[d * 4];
+        if (!(fabs(got - o.g[d]) <= 1e-9 * (1.0 + fabs(o.g[d])))) {
+            const unsigned long long c = atomicAdd(out, 1ull);
+            if (c < 4) {
+                out[1 + 5 * c] = (unsigned long long)t;
+                out[2 + 5 * c] = (unsigned long long)d;
+                out[3 + 5 * c] = (unsigned long long)__double_as_longlong(got);
+                out[4 + 5 * c] = (unsigned long long)__double_as_longlong(o.g[d]);
+                out[5 + 5 * c] = (unsigned long long)slice_len[s];
+            }
+        }
+    }
+}
+__global__ void estep_compare_kernel(const unsigned long long *a, const unsigned long long *b, int64_t n, unsigned long long *out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (a[2 * i] != b[2 * i] || a[2 * i + 1] != b[2 * i + 1]) {
+        const unsigned long long c = atomicAdd(out, 1ull);
+        if (c < 4) {
+            out[1 + 5 * c] = (unsigned long long)i;
+            out[2 + 5 * c] = a[2 * i]; out[3 + 5 * c] = a[2 * i + 1];
+            out[4 + 5 * c] = b[2 * i]; out[5 + 5 * c] = b[2 * i + 1];
+        }
+    }
+}
+int g_opt_debug_estep = 0;
+int debug_estep_check(melissa_handle *h) {
+    Sliced *sl = h->sl;
+    const int64_t NK = (int64_t)h->N * h->K;
+    unsigned long long *dbg = nullptr, *out = nullptr;
+    int rc;
+    if ((rc = dev_alloc(&dbg, 2 * NK)) || (rc = dev_alloc(&out, 32))) return rc;
+    cudaMemsetAsync(dbg, 0, 2 * NK * 8, h->stream);
+    cudaMemsetAsync(out, 0, 32 * 8, h->stream);
+    auto run = [&]() -> int {
+        DISPATCH_D(h->D, estep_check_kernel<DD><<<(unsigned)((sl->S * 32 + 255) / 256), 256, 0, h->stream>>>(
+                             sl->stats, sl->slice_region, sl->lane_cell, h->U, dbg, sl->S * 32, h->K));
+        return MELISSA_OK;
+    };
+    if ((rc = run())) return rc;
+    estep_compare_kernel<<<(unsigned)((NK + 255) / 256), 256, 0, h->stream>>>(h->log_rho_fx, dbg, NK, out);
+    unsigned long long host[32];
+    cudaMemcpyAsync(host, out, sizeof host, cudaMemcpyDeviceToHost, h->stream);
+    cudaStreamSynchronize(h->stream);
+    static int sweep_no = 0;
+    ++sweep_no;
+    if (host[0]) {
+        std::fprintf(stderr, "[debug_estep] sweep %d: %llu of %lld accumulators differ\n", sweep_no, host[0], (long long)NK);
+        for (unsigned long long c = 0; c < host[0] && c < 4; ++c)
+            std::fprintf(stderr, "   cell %lld k %lld  sweep hi=%lld lo=%016llx   check hi=%lld lo=%016llx   diff = %.6e\n",
+                         (long long)(host[1 + 5 * c] / h->K), (long long)(host[1 + 5 * c] % h->K), (long long)host[3 + 5 * c],
+                         host[2 + 5 * c], (long long)host[5 + 5 * c], host[4 + 5 * c],
+                         ((double)(long long)host[3 + 5 * c] - (double)(long long)host[5 + 5 * c]) +
+                             ((double)host[2 + 5 * c] - (double)host[4 + 5 * c]) * 0x1p-64);
+    }
+    // g (note: r is still the r the sweep used: resp_kernel runs later)
+    cudaMemsetAsync(out, 0, 32 * 8, h->stream);
+    auto run2 = [&]() -> int {
+        DISPATCH_D(h->D, g_check_kernel<DD><<<(unsigned)((sl->S * 32 + 255) / 256), 256, 0, h->stream>>>(
+                             sl->x_sell, sl->ybits, sl->slice_xbase, sl->slice_ybase, sl->slice_len, sl->lane_meta, sl->stats,
+                             sl->slice_region, sl->lane_cell, h->U, h->r, out, sl->S * 32, h->K, h->basis));
+        return MELISSA_OK;
+    };
+    if ((rc = run2())) return rc;
+    cudaMemcpyAsync(host, out, sizeof host, cudaMemcpyDeviceToHost, h->stream);
+    cudaStreamSynchronize(h->stream);
+    if (host[0]) {
+        std::fprintf(stderr, "[debug_estep] sweep %d: %llu values of g differ\n", sweep_no, host[0]);
+        for (unsigned long long c = 0; c < host[0] && c < 4; ++c) {
+            double got, want;
+            std::memcpy(&got, &host[3 + 5 * c], 8);
+            std::memcpy(&want, &host[4 + 5 * c], 8);
+            std::fprintf(stderr, "   slice %lld lane %lld d %lld (slice length %lld): sweep %.12g  check %.12g\n",
+                         (long long)(host[1 + 5 * c] >> 5), (long long)(host[1 + 5 * c] & 31), (long long)host[2 + 5 * c],
+                         (long long)host[5 + 5 * c], got, want);
+        }
+    }
+    cudaFree(dbg);
+    cudaFree(out);
+    return MELISSA_OK;
+}
+
 int launch_sweep3(melissa_handle *h, bool with_lb) {
     Sliced *sl = h->sl;
     const int nw = h->sweep_warps;
@@ -1173,6 +1307,7 @@ int launch_sweep3(melissa_handle *h, bool with_lb) {
 #undef SWEEP3
     prof_end(h);
     CU(cudaGetLastError());
+    if (g_opt_debug_estep) return debug_estep_check(h);
     return MELISSA_OK;
 }
 
@@ -1494,6 +1629,10 @@ int melissa_set_option(const char *key, int64_t value) {
         return MELISSA_OK;
     }
     if (!std::strcmp(key, "clusters_hint")) return MELISSA_OK;      // round-1 knob: the layout no longer depends on K
+    if (!std::strcmp(key, "debug_estep")) {
+        g_opt_debug_estep = value != 0;
+        return MELISSA_OK;
+    }
     if (!std::strcmp(key, "sweep_chunk")) {
         if (value < 0 || value > (1 << 20)) return fail(MELISSA_ERR_ARG, "sweep_chunk must be in 0..2^20");
         g_opt_sweep_chunk = (int)value;

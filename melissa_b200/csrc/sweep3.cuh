@@ -134,6 +134,7 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
                 const int ng = (L + XU - 1) / XU;
                 const double *fsrc = xgrp + 64 * (NST - 1);                 // next group to fetch
                 if (pre != NST - 1) {                                       // cold start: nothing usable in flight
+                    __syncwarp();                                           // (every lane is done reading the ring)
                     x_group_wait<0>();
 #pragma unroll
                     for (int gq = 0; gq < NST - 1; ++gq) {                 // (groups past the slice read the slack / the next slice: harmless)
@@ -172,10 +173,18 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
                 unsigned bad = 0;
                 // the slice after this one is prefetched into the ring while this one's last groups are consumed
                 // (n_* already hold its metadata); short slices skip that and start cold
+#ifdef SWEEP3_NOCHAIN
+                const bool chain = false;
+#else
                 const bool chain = has_next && ng >= NST - 1;
+#endif
                 const int i_switch = chain ? XU * (ng - (NST - 1)) : 0x7fffffff;   // from this row on, fetch the next slice
                 for (int i0 = 0; i0 < L; i0 += XU) {
                     if (i0 == i_switch) fsrc = a.x_sell + n_xb + 2 * lane;
+                    // The slot filled now is the one read in the previous trip.  Lanes of a warp need not run
+                    // in lock-step (a lane that is behind would find the NEXT group's bytes in its slot), so
+                    // nobody refills before everybody has read:
+                    __syncwarp();
                     x_group_async(my_x_fill + slot, fsrc);
                     x_group_commit();
                     fsrc += 64;
@@ -183,9 +192,14 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
                     x_group_wait<NST - 1>();
                     __syncwarp();
                     double xa[XU];
+#ifdef SWEEP3_NORING
+#pragma unroll
+                    for (int u = 0; u < XU; ++u) xa[u] = xrow[(int64_t)(i0 + u) * 32];
+#else
 #pragma unroll
                     for (int u = 0; u < XU; ++u)
                         asm volatile("ld.shared.f64 %0, [%1];" : "=d"(xa[u]) : "r"(my_x_read + slot + u * 256) : "memory");
+#endif
                     uint32_t ywn = yw;
                     if (((i0 + XU) & 31) == 0 && i0 + XU < L) ywn = a.ybits[yb + (int64_t)((i0 + XU) >> 5) * 32 + lane];
 #pragma unroll
