@@ -152,15 +152,29 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
                     cur_m = m;
                 }
                 const double *rp = a.r + (int64_t)(valid ? cell : 0) * K;
+                double *rec = a.stats + (int64_t)s * (R * 32) + (lane >> 2) * (R * 4) + (lane & 3);
+                {   // the H^T H part of the record is wanted after the row loop: start it on its way to L2 now
+                    // (the 4 lanes of a record group share its 32-byte rows, so each lane asks for every 4th one)
+                    const double *hrow = rec - (lane & 3) + (D + (lane & 3)) * 4;
+#pragma unroll
+                    for (int q = 0; q < T; q += 4)
+                        if (q + (lane & 3) < T) asm volatile("prefetch.global.L2 [%0];" ::"l"(hrow + q * 4));
+                }
                 double wbar[D];
 #pragma unroll
                 for (int d = 0; d < D; ++d) wbar[d] = 0.0;
-#pragma unroll 2
-                for (int k = 0; k < K; ++k) {
-                    const double rk = valid ? rp[k] : 0.0;
-                    const double *u = my_u + k * R;
+                for (int k0 = 0; k0 < K; k0 += 8) {         // the cell's responsibilities, eight loads in flight at a time
+                    double rk[8];
 #pragma unroll
-                    for (int d = 0; d < D; ++d) wbar[d] = fma(rk, u[d], wbar[d]);
+                    for (int j = 0; j < 8; ++j) rk[j] = (valid && k0 + j < K) ? rp[k0 + j] : 0.0;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        if (k0 + j < K) {
+                            const double *u = my_u + (k0 + j) * R;
+#pragma unroll
+                            for (int d = 0; d < D; ++d) wbar[d] = fma(rk[j], u[d], wbar[d]);
+                        }
+                    }
                 }
                 double g[D];
 #pragma unroll
@@ -242,7 +256,6 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
                     lb_s = o.lb;
                     wrong_s = (int)o.wrong;
                 }
-                double *rec = a.stats + (int64_t)s * (R * 32) + (lane >> 2) * (R * 4) + (lane & 3);
 #pragma unroll
                 for (int d = 0; d < D; ++d) rec[d * 4] = g[d];
                 // E-step terms of the next iteration (R/melissa_vb.R:325-326): U[m,k] . [g | H^T H]
