@@ -1008,7 +1008,7 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
         rt.neg_s = -rt.s;
         rt.mu1 = b.mus[0];
         rt.neg_gamma = -b.gamma;
-        rt.cA = -2.0 * b.gamma * rt.s;                 // -2 gamma u0 = cA j + cB,  u0 = j s - mu_1
+        rt.cA = -2.0 * b.gamma;                        // -2 gamma u0 = cA x0 + cB,  u0 = x0 - mu_1
         rt.cB = 2.0 * b.gamma * rt.mu1;
         rt.g2d = 2.0 * b.gamma * delta;
         rt.q = std::exp(-b.gamma * delta * delta);
@@ -1016,6 +1016,7 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
         const int j_hi = (1 << k) + 1;                 // x in [-1, 1] -> j in [-2^k, 2^k], one guard entry each side
         rt.idx0 = j_hi;
         rt.n_entries = 2 * j_hi + 1;
+        rt.magic = (6755399441055744.0 + (double)j_hi) * rt.s;     // (1.5 * 2^52 + idx0) s, exact
         rbf_tab.resize((size_t)rt.n_entries);
         for (int j = -j_hi; j <= j_hi; ++j) {
             const double u0 = (double)j * rt.s - rt.mu1;

@@ -18,6 +18,7 @@
 struct RbfTab {
     double inv_s, neg_s, neg_gamma, cA, cB, g2d, q2;
     double s, mu1, q;
+    double magic;            // 1.5 * 2^52 s + idx0 s: x + magic has the table index in its low word and (x + magic) - magic = x0
     int n_entries, idx0;
 };
 
@@ -25,6 +26,8 @@ constexpr int MILLS_SP = 512;                 // table points per unit of t
 constexpr int MILLS_HALF = 8 * MILLS_SP;      // t in [-8, 8]
 constexpr int MILLS_N = 2 * MILLS_HALF + 1;
 constexpr double MAGIC = 6755399441055744.0;  // 1.5 * 2^52: (v + MAGIC) - MAGIC rounds v to an integer
+// the same with the scale and the index offset folded in: t + MILLS_MAGIC has round(t * MILLS_SP) + MILLS_HALF in its low word
+constexpr double MILLS_MAGIC = MAGIC / MILLS_SP + (double)MILLS_HALF / MILLS_SP;
 #ifndef SWEEP3_THREADS
 #define SWEEP3_THREADS 768                    // one persistent CTA per SM
 #endif
@@ -95,14 +98,14 @@ __device__ __forceinline__ void rbf_row3(double x, const RbfTab &rt, const doubl
     constexpr int NW = D <= 9 ? 6 : 8;
     h[0] = 1.0;
     if (D == 1) return;
-    const double v = fma(x, rt.inv_s, MAGIC);
-    const int j = __double2loint(v) + rt.idx0;
-    const int jc = min(max(j, 0), rt.n_entries - 1);
-    bad |= (unsigned)(j ^ jc);
-    const double jd = v - MAGIC;
-    const double d = fma(jd, rt.neg_s, x);
+    const double v = x + rt.magic;                                         // low word = table index
+    const unsigned j = (unsigned)__double2loint(v);
+    const unsigned jc = min(j, (unsigned)(rt.n_entries - 1));
+    bad |= j ^ jc;
+    const double x0 = v - rt.magic;
+    const double d = x - x0;
     const double2 eb = tab[jc];
-    const double w = d * fma(rt.neg_gamma, d, fma(jd, rt.cA, rt.cB));      // -gamma d (2 u0 + d)
+    const double w = d * fma(rt.neg_gamma, d, fma(x0, rt.cA, rt.cB));      // -gamma d (2 u0 + d), u0 = x0 - mu_1
     h[1] = eb.x * exp_series<NW>(w);
     if (D > 2) {
         double bj = eb.y * exp_series<NW - 1>(rt.g2d * d);
@@ -121,11 +124,11 @@ __device__ __forceinline__ void rbf_row3(double x, const RbfTab &rt, const doubl
 // against mpmath (tests/test_table_functions.py).  The reciprocal is MUFU.RCP64H (2^-23) plus one
 // cubically convergent step (2^-69).  |t| beyond the table is reported through `bad`.
 __device__ __forceinline__ double trunc_mean3(double t, const double *__restrict__ tab, unsigned &bad, double &R_out) {
-    const double v = fma(t, (double)MILLS_SP, MAGIC);
-    const int i = __double2loint(v) + MILLS_HALF;
-    const int ic = min(max(i, 0), 2 * MILLS_HALF);
-    bad |= (unsigned)(i ^ ic);
-    const double t0 = (v - MAGIC) * (1.0 / MILLS_SP);
+    const double v = t + MILLS_MAGIC;                                      // low word = table index
+    const unsigned i = (unsigned)__double2loint(v);
+    const unsigned ic = min(i, 2u * MILLS_HALF);
+    bad |= i ^ ic;
+    const double t0 = v - MILLS_MAGIC;
     const double d = t - t0;
     const double R0 = tab[ic];
     const double c1 = fma(t0, R0, 1.0);

@@ -86,6 +86,7 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
     const uint32_t my_x_smem = (uint32_t)__cvta_generic_to_shared(s_x + (size_t)warp * NST * XU * 32);
     const uint32_t my_x_fill = my_x_smem + (uint32_t)lane * 16;      // this lane's 16 bytes of a group
     const uint32_t my_x_read = my_x_smem + (uint32_t)lane * 8;       // this lane's CpG of a row
+    const uint32_t rbf_addr = (uint32_t)__cvta_generic_to_shared(s_rbf), mills_addr = (uint32_t)__cvta_generic_to_shared(s_mills);
     uint32_t slot = 0;                                               // byte offset of the next slot to fill
     int pre = 0;
     int cur_m = -1;
@@ -193,55 +194,107 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
                 const bool chain = has_next && ng >= NST - 1;
 #endif
                 const int i_switch = chain ? XU * (ng - (NST - 1)) : 0x7fffffff;   // from this row on, fetch the next slice
-                for (int i0 = 0; i0 < L; i0 += XU) {
-                    if (i0 == i_switch) fsrc = a.x_sell + n_xb + 2 * lane;
-                    // The slot filled now is the one read in the previous trip.  Lanes of a warp need not run
-                    // in lock-step (a lane that is behind would find the NEXT group's bytes in its slot), so
-                    // nobody refills before everybody has read:
-                    __syncwarp();
-                    x_group_async(my_x_fill + slot, fsrc);
-                    x_group_commit();
-                    fsrc += 64;
-                    slot = (slot + SLOT_BYTES) & RING_MASK;                 // = the slot NST - 1 groups back: the one to consume
-                    x_group_wait<NST - 1>();
-                    __syncwarp();
-                    double xa[XU];
+                const double *nsrc = chain ? a.x_sell + n_xb + 2 * lane : fsrc;
+                // methylation states come 32 rows per word: the row loop runs word by word
+                for (int wbase = 0; wbase < L; wbase += 32) {
+                    const int iend = min(wbase + 32, L);
+                    uint32_t ywn = 0;
+                    if (iend < L) ywn = a.ybits[yb + (int64_t)((wbase >> 5) + 1) * 32 + lane];
+                    // bit 31 of ycur = "flip the sign" for the current row (y = 0), shifted up row by row
+                    uint32_t ycur = __brev(~yw);
+                    for (int i0 = wbase; i0 < iend; i0 += XU) {
+                        if (i0 == i_switch) fsrc = nsrc;
+                        // The slot filled now is the one read in the previous trip.  Lanes of a warp need not run
+                        // in lock-step (a lane that is behind would find the NEXT group's bytes in its slot), so
+                        // nobody refills before everybody has read:
+                        __syncwarp();
+                        x_group_async(my_x_fill + slot, fsrc);
+                        x_group_commit();
+                        fsrc += 64;
+                        slot = (slot + SLOT_BYTES) & RING_MASK;             // = the slot NST - 1 groups back: the one to consume
+                        x_group_wait<NST - 1>();
+                        __syncwarp();
+                        double xa[XU];
 #ifdef SWEEP3_NORING
 #pragma unroll
-                    for (int u = 0; u < XU; ++u) xa[u] = xrow[(int64_t)(i0 + u) * 32];
+                        for (int u = 0; u < XU; ++u) xa[u] = xrow[(int64_t)(i0 + u) * 32];
 #else
 #pragma unroll
-                    for (int u = 0; u < XU; ++u)
-                        asm volatile("ld.shared.f64 %0, [%1];" : "=d"(xa[u]) : "r"(my_x_read + slot + u * 256) : "memory");
+                        for (int u = 0; u < XU; ++u)
+                            asm volatile("ld.shared.f64 %0, [%1];" : "=d"(xa[u]) : "r"(my_x_read + slot + u * 256) : "memory");
 #endif
-                    uint32_t ywn = yw;
-                    if (((i0 + XU) & 31) == 0 && i0 + XU < L) ywn = a.ybits[yb + (int64_t)((i0 + XU) >> 5) * 32 + lane];
 #pragma unroll
-                    for (int u = 0; u < XU; ++u) {
-                        const int i = i0 + u;
-                        const uint32_t sflip = (((yw >> (i & 31)) & 1u) ^ 1u) << 31;      // s = +1 for y = 1, -1 for y = 0
-                        double h[D];
-                        unsigned bad_row = 0;
-                        rbf_row3<D>(xa[u], a.rt, s_rbf, h, bad_row);
-                        double mu = wbar[0];
+                        for (int u = 0; u < XU; ++u) {
+                            const int i = i0 + u;
+                            const uint32_t yu = ycur << u;
+                            // ---- RBF row (see rbf_row3 in sliced.cuh for the maths; here with the grid offset folded
+                            //      into the rounding constant and shared-memory addresses instead of pointers)
+                            double h[D];
+                            unsigned bad_row = 0;
+                            h[0] = 1.0;
+                            if (D > 1) {
+                                constexpr int NW = D <= 9 ? 6 : 8;
+                                const double v = xa[u] + a.rt.magic;                       // low word = table index
+                                const unsigned j = (unsigned)__double2loint(v);
+                                const unsigned jc = min(j, (unsigned)(a.rt.n_entries - 1));
+                                bad_row = j ^ jc;
+                                const double x0 = v - a.rt.magic;
+                                const double dx = xa[u] - x0;
+                                double e0, b0;
+                                asm("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(e0), "=d"(b0) : "r"(rbf_addr + jc * 16));
+                                const double w = dx * fma(a.rt.neg_gamma, dx, fma(x0, a.rt.cA, a.rt.cB));
+                                h[1] = e0 * exp_series<NW>(w);
+                                if (D > 2) {
+                                    double bj = b0 * exp_series<NW - 1>(a.rt.g2d * dx);
 #pragma unroll
-                        for (int d = 1; d < D; ++d) mu = fma(h[d], wbar[d], mu);
-                        const double t = __hiloint2double(__double2hiint(mu) ^ sflip, __double2loint(mu));
-                        double Rt;
-                        const double Gt = trunc_mean3(t, s_mills, bad_row, Rt);
-                        const double Ez = __hiloint2double(__double2hiint(Gt) ^ sflip, __double2loint(Gt));
-                        if (i < len) {
-                            bad |= bad_row;
-                            g[0] += Ez;
+                                    for (int q = 2; q < D; ++q) {
+                                        h[q] = h[q - 1] * bj;
+                                        if (q + 1 < D) bj *= a.rt.q2;
+                                    }
+                                }
+                            }
+                            double mu = wbar[0];
 #pragma unroll
-                            for (int d = 1; d < D; ++d) g[d] = fma(h[d], Ez, g[d]);
-                            if (WITH_LB) {
-                                // log(Phi(s mu) + 1e-10): both branches of R/melissa_vb.R:471-472 reduce to it, and
-                                // Phi = R * phi with the R the E[z] evaluation just produced (one exp + one log)
-                                lb_s += fma(0.5 * mu, mu, log(fma(Rt, 0.39894228040143267794 * exp(-0.5 * t * t), 1e-10)));
-                                wrong_s += t < -5.0;
+                            for (int d = 1; d < D; ++d) mu = fma(h[d], wbar[d], mu);
+                            // t = s mu, s = +1 for y = 1 and -1 for y = 0: one three-input logic op on the high word
+                            const double t = __hiloint2double(__double2hiint(mu) ^ (int)(yu & 0x80000000u), __double2loint(mu));
+                            // ---- E[z | z > 0] = t + 1 / R(t) (trunc_mean3 in sliced.cuh)
+                            const double vt = t + MILLS_MAGIC;                             // low word = table index
+                            const unsigned it = (unsigned)__double2loint(vt);
+                            const unsigned ic = min(it, 2u * MILLS_HALF);
+                            bad_row |= it ^ ic;
+                            const double t0 = vt - MILLS_MAGIC;
+                            const double dt = t - t0;
+                            double R0;
+                            asm("ld.shared.f64 %0, [%1];" : "=d"(R0) : "r"(mills_addr + ic * 8));
+                            const double c1 = fma(t0, R0, 1.0);
+                            const double c2 = 0.5 * fma(t0, c1, R0);
+                            const double c3 = fma(t0, c2, c1) * kInvInt(3);
+                            const double c4 = 0.25 * fma(t0, c3, c2);
+                            double Rt = fma(dt, c4, c3);
+                            Rt = fma(dt, Rt, c2);
+                            Rt = fma(dt, Rt, c1);
+                            Rt = fma(dt, Rt, R0);
+                            double y;
+                            asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(Rt));
+                            const double e = fma(-Rt, y, 1.0);
+                            y = fma(y, fma(e, e, e), y);
+                            const double Gt = t + y;
+                            const double Ez = __hiloint2double(__double2hiint(Gt) ^ (int)(yu & 0x80000000u), __double2loint(Gt));
+                            if (i < len) {
+                                bad |= bad_row;
+                                g[0] += Ez;
+#pragma unroll
+                                for (int d = 1; d < D; ++d) g[d] = fma(h[d], Ez, g[d]);
+                                if (WITH_LB) {
+                                    // log(Phi(s mu) + 1e-10): both branches of R/melissa_vb.R:471-472 reduce to it, and
+                                    // Phi = R * phi with the R the E[z] evaluation just produced (one exp + one log)
+                                    lb_s += fma(0.5 * mu, mu, log(fma(Rt, 0.39894228040143267794 * exp(-0.5 * t * t), 1e-10)));
+                                    wrong_s += t < -5.0;
+                                }
                             }
                         }
+                        ycur <<= XU;
                     }
                     yw = ywn;
                 }
