@@ -43,13 +43,15 @@ struct Sweep3Args {
 #ifndef SWEEP3_NST
 #define SWEEP3_NST 4          // groups of the x ring per warp: NST - 1 groups (6 rows) are in flight ahead of the arithmetic
 #endif
-static_assert(SWEEP3_XU == 2, "the x ring moves two rows per cp.async");
+static_assert(SWEEP3_XU % 2 == 0, "the x ring moves two rows per cp.async");
 static_assert((SWEEP3_NST & (SWEEP3_NST - 1)) == 0, "ring size must be a power of two");
 
 // One group of x (rows 2g, 2g + 1 of a slice: 512 contiguous bytes) global -> shared, no registers
 // involved: lanes 0-15 move the first row, lanes 16-31 the second, 16 bytes each, bypassing L1.
 __device__ __forceinline__ void x_group_async(uint32_t dst_smem, const double *src) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_smem), "l"(src) : "memory");
+#pragma unroll
+    for (int c = 0; c < SWEEP3_XU / 2; ++c)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_smem + c * 512), "l"(src + c * 64) : "memory");
 }
 __device__ __forceinline__ void x_group_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
@@ -131,15 +133,15 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
                 const int len = meta & 0xffff, nl = meta >> 16;
                 const bool valid = cell >= 0;
                 const double *xrow = a.x_sell + xb + lane;
-                const double *xgrp = a.x_sell + xb + 2 * lane;              // + 64 g: this lane's 16 bytes of group g
+                const double *xgrp = a.x_sell + xb + 2 * lane;              // + 32 XU g: this lane's 16 bytes of each row pair of group g
                 const int ng = (L + XU - 1) / XU;
-                const double *fsrc = xgrp + 64 * (NST - 1);                 // next group to fetch
+                const double *fsrc = xgrp + 32 * XU * (NST - 1);            // next group to fetch
                 if (pre != NST - 1) {                                       // cold start: nothing usable in flight
                     __syncwarp();                                           // (every lane is done reading the ring)
                     x_group_wait<0>();
 #pragma unroll
                     for (int gq = 0; gq < NST - 1; ++gq) {                 // (groups past the slice read the slack / the next slice: harmless)
-                        x_group_async(my_x_fill + slot, xgrp + 64 * gq);
+                        x_group_async(my_x_fill + slot, xgrp + 32 * XU * gq);
                         x_group_commit();
                         slot = (slot + SLOT_BYTES) & RING_MASK;
                     }
@@ -210,7 +212,7 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
                         __syncwarp();
                         x_group_async(my_x_fill + slot, fsrc);
                         x_group_commit();
-                        fsrc += 64;
+                        fsrc += 32 * XU;
                         slot = (slot + SLOT_BYTES) & RING_MASK;             // = the slot NST - 1 groups back: the one to consume
                         x_group_wait<NST - 1>();
                         __syncwarp();
