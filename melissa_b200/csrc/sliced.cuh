@@ -51,6 +51,7 @@ struct Sliced {
     double *mills_tab = nullptr;          // [MILLS_N]
     double2 *rbf_tab = nullptr;           // [rt.n_entries] (E(u0), q B(u0))
     RbfTab rt{};
+    int32_t *slice_rec = nullptr;         // [S][SREC_WORDS] everything the sweep needs to know about a slice, in one record (sweep3.cuh)
     int32_t *chunk_ptr = nullptr;         // [NC + 1] first slice of each chunk of the sweep
     int NC = 0;
     unsigned int *chunk_counter = nullptr;         // chunk dispenser of the persistent sweep
