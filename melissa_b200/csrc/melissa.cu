@@ -883,7 +883,7 @@ void free_sliced(melissa_handle *h) {
     cudaFree(sl->slice_len); cudaFree(sl->slice_region); cudaFree(sl->slice_cb); cudaFree(sl->lane_cell);
     cudaFree(sl->lane_meta); cudaFree(sl->lane_pair); cudaFree(sl->blk_cells); cudaFree(sl->reg_slice_ptr);
     cudaFree(sl->reg_slice); cudaFree(sl->stats); cudaFree(sl->mills_tab); cudaFree(sl->rbf_tab);
-    cudaFree(sl->chunk_ptr); cudaFree(sl->chunk_counter); cudaFree(sl->slice_rec);
+    cudaFree(sl->chunk_ptr); cudaFree(sl->chunk_counter);
     delete sl;
     h->sl = nullptr;
 }
@@ -1109,10 +1109,7 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
         if ((rc = run())) { cudaFree(d_src); return rc; }
     }
     mills_table_kernel<<<(MILLS_N + 255) / 256, 256>>>(sl->mills_tab);
-    if ((rc = dev_alloc(&sl->slice_rec, S * SREC_WORDS))) { cudaFree(d_src); return rc; }
-    slice_rec_kernel<<<grid, 256>>>(sl->slice_xbase, sl->slice_ybase, sl->slice_len, sl->slice_region, sl->slice_cb,
-                                    sl->lane_cell, sl->lane_meta, sl->ybits, sl->slice_rec, S);
-    h->launches += 4;
+    h->launches += 3;
     const cudaError_t e = cudaDeviceSynchronize();
     cudaFree(d_src);
     if (e != cudaSuccess) return fail(MELISSA_ERR_CUDA, "sliced layout build failed: %s", cudaGetErrorString(e));
@@ -1128,7 +1125,7 @@ size_t sweep3_smem(const melissa_handle *h, int nw) {
     const size_t UR = ((size_t)h->K * h->R + 1) & ~(size_t)1;
     return (size_t)sl->rt.n_entries * sizeof(double2) + ((size_t)MILLS_N + 1) * sizeof(double) +
            4 * (size_t)sl->Tn * h->K * sizeof(unsigned int) + (size_t)nw * UR * sizeof(double) +
-           (size_t)nw * SWEEP3_NST * SWEEP3_XU * 32 * sizeof(double) + (size_t)nw * SREC_WORDS * sizeof(int32_t) + 4 * 8 + 16;
+           (size_t)nw * SWEEP3_NST * SWEEP3_XU * 32 * sizeof(double) + 4 * 8 + 16;
 }
 
 // Most warps (of SWEEP3_THREADS / 32) whose staging areas still fit next to the rest; 0 = not even four.
@@ -1160,10 +1157,14 @@ __global__ void estep_check_kernel(const double *__restrict__ stats, const int32
     const double *rec = stats + s * (R * 32) + (lane >> 2) * (R * 4) + (lane & 3);
     for (int k = 0; k < K; ++k) {
         const double *u = U + ((int64_t)m * K + k) * R;
-        double trc = 0.0, lin = 0.0;
-        for (int q = 0; q < T; ++q) trc = fma(u[D + q], rec[(D + q) * 4], trc);
+        double t0 = 0.0, t1 = 0.0, t2 = 0.0, lin = 0.0;       // the sweep's order of operations
+        for (int q = 0; q < T; q += 3) {
+            t0 = fma(u[D + q], rec[(D + q) * 4], t0);
+            if (q + 1 < T) t1 = fma(u[D + q + 1], rec[(D + q + 1) * 4], t1);
+            if (q + 2 < T) t2 = fma(u[D + q + 2], rec[(D + q + 2) * 4], t2);
+        }
         for (int d = 0; d < D; ++d) lin = fma(u[d], rec[d * 4], lin);
-        const double v = lin + trc;
+        const double v = lin + ((t0 + t1) + t2);
         // same 2^-44 image as the sweep's limbs
         const double f = floor(v * 0x1p44);
         const long long hi = (long long)floor(f * 0x1p-44);
@@ -1286,7 +1287,9 @@ int launch_sweep3(melissa_handle *h, bool with_lb) {
                     "pack with a smaller \"cell_block\" option", h->K, sl->Tn);
     const size_t smem = sweep3_smem(h, nw);
     Sweep3Args a;
-    a.x_sell = sl->x_sell; a.ybits = sl->ybits; a.slice_rec = sl->slice_rec; a.blk_cells = sl->blk_cells;
+    a.x_sell = sl->x_sell; a.ybits = sl->ybits; a.slice_xbase = sl->slice_xbase; a.slice_ybase = sl->slice_ybase;
+    a.slice_len = sl->slice_len; a.slice_region = sl->slice_region; a.slice_cb = sl->slice_cb;
+    a.lane_cell = sl->lane_cell; a.lane_meta = sl->lane_meta; a.blk_cells = sl->blk_cells;
     a.chunk_ptr = sl->chunk_ptr; a.stats = sl->stats; a.U = h->U; a.r = h->r;
     a.log_rho_fx = h->log_rho_fx; a.lb_fx = h->lb_fx; a.poison = h->poison;
     a.mills_tab = sl->mills_tab; a.rbf_tab = sl->rbf_tab; a.rt = sl->rt; a.basis = h->basis;

@@ -18,16 +18,11 @@
 // Included from melissa.cu inside its anonymous namespace, after sliced.cuh.
 #pragma once
 
-// Per-slice record of the sweep, 416 bytes, fetched with one cp.async per lane (lanes 0-25):
-//   words 0-1 x offset (int64) | 2-3 y offset (int64) | 4 rows L | 5 region | 6 cell block | 7 -
-//   8-39 cell of every lane | 40-71 CpG count | block position << 16 of every lane | 72-103 first word of y bits
-constexpr int SREC_WORDS = 104;
-
 struct Sweep3Args {
     const double *x_sell;
     const uint32_t *ybits;
-    const int32_t *slice_rec;                 // [S][SREC_WORDS]
-    const int32_t *blk_cells;
+    const int64_t *slice_xbase, *slice_ybase;
+    const int32_t *slice_len, *slice_region, *slice_cb, *lane_cell, *lane_meta, *blk_cells;
     const int32_t *chunk_ptr;                 // [NC + 1] first slice of every chunk; a chunk stays inside one cell block
     double *stats;
     const double *U, *r;
@@ -43,43 +38,24 @@ struct Sweep3Args {
 };
 
 #ifndef SWEEP3_XU
-#define SWEEP3_XU 2           // CpG rows per group of the x ring
+#define SWEEP3_XU 2           // CpG rows per group: one 16-byte cp.async per lane moves a group (2 rows x 256 bytes)
 #endif
 #ifndef SWEEP3_NST
-#define SWEEP3_NST 4          // groups of the x ring per warp: NST - 1 groups are in flight ahead of the arithmetic
+#define SWEEP3_NST 4          // groups of the x ring per warp: NST - 1 groups (6 rows) are in flight ahead of the arithmetic
 #endif
 static_assert(SWEEP3_XU % 2 == 0, "the x ring moves two rows per cp.async");
 static_assert((SWEEP3_NST & (SWEEP3_NST - 1)) == 0, "ring size must be a power of two");
 
-// Everything a warp needs from global memory for a slice -- its record, the q(w) block U[m], the x rows -- travels
-// global -> shared with cp.async: no registers are tied up while the data is on its way (ptxas otherwise sinks
-// "prefetching" loads to their first use, which is what ncu showed for the first version of this kernel), and all
-// of it shares one sequence of commit groups, so cp.async.wait_group tells when each piece has landed.
-__device__ __forceinline__ void cp_async16(uint32_t dst_smem, const void *src) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_smem), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async8(uint32_t dst_smem, const void *src) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst_smem), "l"(src) : "memory");
-}
-// one group of x (XU rows of a slice: XU x 256 contiguous bytes): lanes 0-15 move the first row of each row pair,
-// lanes 16-31 the second, 16 bytes each, bypassing L1
+// One group of x (rows 2g, 2g + 1 of a slice: 512 contiguous bytes) global -> shared, no registers
+// involved: lanes 0-15 move the first row, lanes 16-31 the second, 16 bytes each, bypassing L1.
 __device__ __forceinline__ void x_group_async(uint32_t dst_smem, const double *src) {
 #pragma unroll
-    for (int c = 0; c < SWEEP3_XU / 2; ++c) cp_async16(dst_smem + c * 512, src + c * 64);
+    for (int c = 0; c < SWEEP3_XU / 2; ++c)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_smem + c * 512), "l"(src + c * 64) : "memory");
 }
 __device__ __forceinline__ void x_group_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void x_group_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-__device__ __forceinline__ int lds_i32(uint32_t addr) {
-    int v;
-    asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
-    return v;
-}
-__device__ __forceinline__ long long lds_i64(uint32_t addr) {
-    long long v;
-    asm volatile("ld.shared.s64 %0, [%1];" : "=l"(v) : "r"(addr) : "memory");
-    return v;
-}
 
 template <int D, bool WITH_LB>
 __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a) {
@@ -89,14 +65,13 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
     const int K = a.K, Tn = a.Tn;
     const int nw = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int UR = (K * R + 1) & ~1;
-    // shared: rbf table | mills table | block sums (limbs) | per-warp U[m] | per-warp x ring | per-warp slice record | lb sums | control words
+    // shared: rbf table | mills table | block sums (fixed point) | per-warp U[m] | lb sums | control words
     double2 *s_rbf = reinterpret_cast<double2 *>(smem_raw);
     double *s_mills = reinterpret_cast<double *>(s_rbf + a.rt.n_entries);
     unsigned int *s_acc = reinterpret_cast<unsigned int *>(s_mills + MILLS_N + 1);      // [4 limbs][K][Tn]
     double *s_u = reinterpret_cast<double *>(s_acc + 4 * (size_t)Tn * K);
-    double *s_x = s_u + (size_t)nw * UR;
-    int32_t *s_rec = reinterpret_cast<int32_t *>(s_x + (size_t)nw * NST * XU * 32);
-    unsigned long long *s_lb = reinterpret_cast<unsigned long long *>(s_rec + (size_t)nw * SREC_WORDS);    // [2] + wrong-side count
+    double *s_x = s_u + (size_t)nw * UR;                                                         // per-warp ring of x groups
+    unsigned long long *s_lb = reinterpret_cast<unsigned long long *>(s_x + (size_t)nw * NST * XU * 32);   // [2] + wrong-side count
     int *s_ctl = reinterpret_cast<int *>(s_lb + 4);                                             // cursor, next chunk
     for (int i = threadIdx.x; i < a.rt.n_entries; i += blockDim.x) s_rbf[i] = a.rbf_tab[i];
     for (int i = threadIdx.x; i < MILLS_N; i += blockDim.x) s_mills[i] = a.mills_tab[i];
@@ -104,29 +79,24 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
     if (threadIdx.x < 4) s_lb[threadIdx.x] = 0ull;
     if (threadIdx.x == 0) s_ctl[1] = (int)atomicAdd(a.chunk_counter, 1u);
     __syncthreads();
-    const double *my_u = s_u + (size_t)warp * UR;
-    const uint32_t my_u_smem = (uint32_t)__cvta_generic_to_shared(my_u);
-    // x ring of this warp.  Groups are issued and consumed strictly in order; NST - 1 groups are always
-    // between the issue and the consume position, so one slot offset serves both.  Between slices the
-    // NST - 1 groups in flight belong to the slice that comes next (`pre`), so that a slice does not
-    // start with an empty pipeline.
+    double *my_u = s_u + (size_t)warp * UR;
+    // x ring of this warp.  Groups are issued and consumed strictly in order: `iss` / `con` count them,
+    // slot = counter mod NST.  Between slices NST - 1 groups stay in flight (`pre` of them belong to the
+    // slice that comes next), so that a slice does not start with an empty pipeline.
+    // (NST - 1 groups are always between the issue and the consume position, so one slot offset serves both.)
     constexpr uint32_t SLOT_BYTES = XU * 256, RING_MASK = (NST - 1) * SLOT_BYTES;
     const uint32_t my_x_smem = (uint32_t)__cvta_generic_to_shared(s_x + (size_t)warp * NST * XU * 32);
     const uint32_t my_x_fill = my_x_smem + (uint32_t)lane * 16;      // this lane's 16 bytes of a group
     const uint32_t my_x_read = my_x_smem + (uint32_t)lane * 8;       // this lane's CpG of a row
-    const uint32_t my_rec = (uint32_t)__cvta_generic_to_shared(s_rec + (size_t)warp * SREC_WORDS);
     const uint32_t rbf_addr = (uint32_t)__cvta_generic_to_shared(s_rbf), mills_addr = (uint32_t)__cvta_generic_to_shared(s_mills);
     uint32_t slot = 0;                                               // byte offset of the next slot to fill
     int pre = 0;
     int cur_m = -1;
     int chunk = s_ctl[1];
     const int G = a.G;
-    auto issue_rec = [&](int s) {                                    // record of slice s -> this warp's record buffer
-        if (lane < SREC_WORDS / 4) cp_async16(my_rec + lane * 16, a.slice_rec + (int64_t)s * SREC_WORDS + lane * 4);
-    };
     while (chunk < a.NC) {
         const int c_beg = a.chunk_ptr[chunk], c_end = a.chunk_ptr[chunk + 1];
-        const int cb = a.slice_rec[(int64_t)c_beg * SREC_WORDS + 6];
+        const int cb = a.slice_cb[c_beg];
         __syncthreads();                                   // everybody has read s_ctl[1]; the last flush is done
         if (threadIdx.x == 0) {
             s_ctl[0] = c_beg;
@@ -139,48 +109,35 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
             return __shfl_sync(0xffffffffu, c, 0);
         };
         int run = claim();
-        bool rec_ready = false;                            // is the record in my_rec known to have landed?
-        if (run < c_end) {
-            __syncwarp();
-            issue_rec(run);
-            x_group_commit();
-        }
+        // slice metadata is fetched one slice ahead
+        int n_m = 0, n_L = 0, n_cell = -1, n_meta = 0;
+        int64_t n_xb = 0, n_yb = 0;
+        auto fetch_meta = [&](int s) {
+            n_m = a.slice_region[s]; n_L = a.slice_len[s];
+            n_xb = a.slice_xbase[s]; n_yb = a.slice_ybase[s];
+            n_cell = a.lane_cell[(int64_t)s * 32 + lane]; n_meta = a.lane_meta[(int64_t)s * 32 + lane];
+        };
+        if (run < c_end) fetch_meta(run);
         while (run < c_end) {
             const int run_following = claim();
             const int run_end = min(run + G, c_end);
             for (int s = run; s < run_end; ++s) {
-                // ---- this slice's record (landed, or wait for it), then the buffer goes to the next slice's
-                if (!rec_ready) x_group_wait<0>();
-                __syncwarp();
-                const int64_t xb = lds_i64(my_rec), yb = lds_i64(my_rec + 8);
-                const int L = lds_i32(my_rec + 16), m = lds_i32(my_rec + 20);
-                const int cell = lds_i32(my_rec + 32 + lane * 4), meta = lds_i32(my_rec + 160 + lane * 4);
-                uint32_t yw = (uint32_t)lds_i32(my_rec + 288 + lane * 4);
-                __syncwarp();
+                const int m = n_m, L = n_L, cell = n_cell, meta = n_meta;
+                const int64_t xb = n_xb, yb = n_yb;
                 bool has_next;
                 {
                     const int s_next = s + 1 < run_end ? s + 1 : run_following;
                     has_next = s_next < c_end;
-                    if (has_next) issue_rec(s_next);        // joins the next commit group
+                    if (has_next) fetch_meta(s_next);
                 }
                 const int len = meta & 0xffff, nl = meta >> 16;
                 const bool valid = cell >= 0;
                 const double *xrow = a.x_sell + xb + lane;
                 const double *xgrp = a.x_sell + xb + 2 * lane;              // + 32 XU g: this lane's 16 bytes of each row pair of group g
                 const int ng = (L + XU - 1) / XU;
-                const double *Um = a.U + (int64_t)m * K * R;
-                const bool stage_u = m != cur_m;                            // consecutive slices of a run mostly share the region
-                if (stage_u) {                                              // U[m] -> shared (for the E-step terms after the row loop)
-                    if ((K * R) % 2 == 0) {
-                        for (int i = 2 * lane; i < K * R; i += 64) cp_async16(my_u_smem + i * 8, Um + i);
-                    } else {
-                        for (int i = lane; i < K * R; i += 32) cp_async8(my_u_smem + i * 8, Um + i);
-                    }
-                    cur_m = m;
-                }
-                const bool cold = pre != NST - 1;
                 const double *fsrc = xgrp + 32 * XU * (NST - 1);            // next group to fetch
-                if (cold) {                                                 // nothing usable in flight
+                if (pre != NST - 1) {                                       // cold start: nothing usable in flight
+                    __syncwarp();                                           // (every lane is done reading the ring)
                     x_group_wait<0>();
 #pragma unroll
                     for (int gq = 0; gq < NST - 1; ++gq) {                 // (groups past the slice read the slack / the next slice: harmless)
@@ -189,9 +146,14 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
                         slot = (slot + SLOT_BYTES) & RING_MASK;
                     }
                 }
-                // what was issued above (next record, U[m]) sits in the first group committed in this slice; it has
-                // landed for sure once NST - 1 younger groups have been committed and a wait has followed:
-                const bool early_ready = cold || ng >= NST;                 // ... by the end of the row loop
+                uint32_t yw = a.ybits[yb + lane];
+                if (m != cur_m) {                           // consecutive slices of a run mostly share the region
+                    __syncwarp();
+                    const double *src = a.U + (int64_t)m * K * R;
+                    for (int i = lane; i < K * R; i += 32) my_u[i] = src[i];
+                    __syncwarp();
+                    cur_m = m;
+                }
                 const double *rp = a.r + (int64_t)(valid ? cell : 0) * K;
                 double *rec = a.stats + (int64_t)s * (R * 32) + (lane >> 2) * (R * 4) + (lane & 3);
                 {   // the H^T H part of the record is wanted after the row loop: start it on its way to L2 now
@@ -201,21 +163,19 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
                     for (int q = 0; q < T; q += 4)
                         if (q + (lane & 3) < T) asm volatile("prefetch.global.L2 [%0];" ::"l"(hrow + q * 4));
                 }
-                // mean of w under the cell's responsibilities; the means come straight from global memory (the same
-                // address for every lane), in one batch with the responsibilities
                 double wbar[D];
 #pragma unroll
                 for (int d = 0; d < D; ++d) wbar[d] = 0.0;
-                for (int k0 = 0; k0 < K; k0 += 8) {
+                for (int k0 = 0; k0 < K; k0 += 8) {         // the cell's responsibilities, eight loads in flight at a time
                     double rk[8];
 #pragma unroll
                     for (int j = 0; j < 8; ++j) rk[j] = (valid && k0 + j < K) ? rp[k0 + j] : 0.0;
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
                         if (k0 + j < K) {
-                            const double *u = Um + (k0 + j) * R;
+                            const double *u = my_u + (k0 + j) * R;
 #pragma unroll
-                            for (int d = 0; d < D; ++d) wbar[d] = fma(rk[j], __ldg(u + d), wbar[d]);
+                            for (int d = 0; d < D; ++d) wbar[d] = fma(rk[j], u[d], wbar[d]);
                         }
                     }
                 }
@@ -223,18 +183,20 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
 #pragma unroll
                 for (int d = 0; d < D; ++d) g[d] = 0.0;
                 // Rows past a lane's own length contribute nothing (predicated), rows past L (read from
-                // whatever follows in x_sell, which is over-allocated) are past every lane's length.
+                // whatever follows in x_sell, which is over-allocated by two groups) are past every lane's
+                // length, so each group runs all XU rows with no trip-count test and no predicated load.
                 double lb_s = 0.0;
                 int wrong_s = 0;
                 unsigned bad = 0;
-                // the slice after this one is prefetched into the ring while this one's last groups are consumed; its
-                // x offset is read from its record, which must have landed by then (see above)
+                // the slice after this one is prefetched into the ring while this one's last groups are consumed
+                // (n_* already hold its metadata); short slices skip that and start cold
 #ifdef SWEEP3_NOCHAIN
                 const bool chain = false;
 #else
-                const bool chain = has_next && ng >= (cold ? NST : 2 * NST - 1);
+                const bool chain = has_next && ng >= NST - 1;
 #endif
                 const int i_switch = chain ? XU * (ng - (NST - 1)) : 0x7fffffff;   // from this row on, fetch the next slice
+                const double *nsrc = chain ? a.x_sell + n_xb + 2 * lane : fsrc;
                 // methylation states come 32 rows per word: the row loop runs word by word
                 for (int wbase = 0; wbase < L; wbase += 32) {
                     const int iend = min(wbase + 32, L);
@@ -243,11 +205,11 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
                     // bit 31 of ycur = "flip the sign" for the current row (y = 0), shifted up row by row
                     uint32_t ycur = __brev(~yw);
                     for (int i0 = wbase; i0 < iend; i0 += XU) {
+                        if (i0 == i_switch) fsrc = nsrc;
                         // The slot filled now is the one read in the previous trip.  Lanes of a warp need not run
                         // in lock-step (a lane that is behind would find the NEXT group's bytes in its slot), so
                         // nobody refills before everybody has read:
                         __syncwarp();
-                        if (i0 == i_switch) fsrc = a.x_sell + lds_i64(my_rec) + 2 * lane;
                         x_group_async(my_x_fill + slot, fsrc);
                         x_group_commit();
                         fsrc += 32 * XU;
@@ -339,7 +301,6 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
                     yw = ywn;
                 }
                 pre = chain ? NST - 1 : 0;
-                rec_ready = early_ready;
                 if (__any_sync(0xffffffffu, bad != 0)) {                   // never taken on sane data
                     WBar<D> wb;
 #pragma unroll
@@ -356,11 +317,6 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
                 double hh[T];
 #pragma unroll
                 for (int q = 0; q < T; ++q) hh[q] = rec[(D + q) * 4];
-                if (stage_u && !early_ready) {                              // short slice: U[m] may still be on its way
-                    x_group_wait<0>();
-                    rec_ready = true;
-                }
-                __syncwarp();                                               // U[m] as copied by the other lanes
                 if (valid) {
                     unsigned int *acc = s_acc + nl;
                     bool over = false;
@@ -426,7 +382,6 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
         }
         chunk = chunk_next;
     }
-    x_group_wait<0>();
     if (WITH_LB) {
         __syncthreads();
         if (threadIdx.x == 0) {
@@ -437,30 +392,6 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
             if (s_lb[2]) atomicAdd(a.lb_fx + 2, s_lb[2]);
         }
     }
-}
-
-// The per-slice records of the sweep from the separate index arrays (pack time).
-__global__ void slice_rec_kernel(const int64_t *__restrict__ slice_xbase, const int64_t *__restrict__ slice_ybase,
-                                 const int32_t *__restrict__ slice_len, const int32_t *__restrict__ slice_region,
-                                 const int32_t *__restrict__ slice_cb, const int32_t *__restrict__ lane_cell,
-                                 const int32_t *__restrict__ lane_meta, const uint32_t *__restrict__ ybits,
-                                 int32_t *__restrict__ recs, int64_t S) {
-    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= S * 32) return;
-    const int64_t s = t >> 5;
-    const int lane = (int)(t & 31);
-    int32_t *r = recs + s * SREC_WORDS;
-    if (lane == 0) {
-        reinterpret_cast<int64_t *>(r)[0] = slice_xbase[s];
-        reinterpret_cast<int64_t *>(r)[1] = slice_ybase[s];
-        r[4] = slice_len[s];
-        r[5] = slice_region[s];
-        r[6] = slice_cb[s];
-        r[7] = 0;
-    }
-    r[8 + lane] = lane_cell[t];
-    r[40 + lane] = lane_meta[t];
-    r[72 + lane] = (int32_t)ybits[slice_ybase[s] + lane];
 }
 
 // lb_fx -> lbbuf (doubles, the all-reduce payload of bound iterations), then clear.
