@@ -84,11 +84,20 @@ def algorithmic_bytes(nnz, P, D):
     return 9 * nnz + P * (16 * D + 8)
 
 
+def host_cores():
+    """Cores this process may use.  torchrun exports OMP_NUM_THREADS=1; the CPU arm must not inherit that."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def cpu_port_run(sample, K, basis, w0, steps, warmup, threads=0):
     """The plain-C restatement of the reference loop (oracle/), timed on host cores."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import numpy as np
     import c_oracle
+    threads = threads or host_cores()
     delta_0 = np.full(K, 0.51)
     if warmup > 0:
         c_oracle.vb_run(sample, K, basis, w0, delta_0, vb_max_iter=warmup + 1, n_threads=threads)
@@ -96,6 +105,27 @@ def cpu_port_run(sample, K, basis, w0, steps, warmup, threads=0):
     P = int(sample["pair_cell"].shape[0])
     iters = o["n_iter"] - 1
     return dict(value=P * iters / o["loop_seconds"], seconds=o["loop_seconds"], iters=iters, cores=o["threads"], P=P)
+
+
+def cpu_sample(wl, n_cells):
+    """The first n_cells cells of the workload's recipe as host arrays + initial w (drawn on the GPU when there is one:
+    the NumPy generator needs minutes for a sample of this size)."""
+    from melissa_b200 import synth
+    try:
+        import torch
+        if torch.cuda.is_available():
+            d, tr = synth.generate_device(n_cells, wl["M"], wl["K"], n_basis=wl["n_basis"], seed=wl["seed"], N_total=n_cells,
+                                          chunk_cells=CHUNK)
+            return host_sample(d, n_cells), tr
+    except Exception:
+        pass
+    d, tr = synth.generate(n_cells, wl["M"], wl["K"], n_basis=wl["n_basis"], seed=wl["seed"], N_total=n_cells)
+    return d.as_dict(), tr
+
+
+def default_sample_cells(wl):
+    """~5e6 pairs: 13 iterations of the C restatement take 10-30 s on 16-32 cores, its design matrices ~1 GB."""
+    return max(40, min(wl["N"], int(5.0e6 / wl["M"])))
 
 
 def host_sample(data_t, n_cells):
@@ -137,11 +167,13 @@ def main():
         # every host thread), on a bounded sample of the same workload.  Rank 0 only.
         if rank != 0:
             return
-        from melissa_b200 import synth
-        n_s = args.cpu_sample_cells or max(40, min(wl["N"], int(2.0e6 / wl["M"])))
-        d, tr = synth.generate(n_s, wl["M"], K, n_basis=wl["n_basis"], seed=wl["seed"], N_total=n_s)
-        r = cpu_port_run(d.as_dict(), K, tr["basis"], tr["w0"], steps, warmup)
+        n_s = args.cpu_sample_cells or default_sample_cells(wl)
+        d, tr = cpu_sample(wl, n_s)
+        r = cpu_port_run(d, K, tr["basis"], tr["w0"], steps, warmup)
         sample = "%d cells x %d regions (%d pairs) of the same recipe, %d iterations" % (n_s, wl["M"], r["P"], r["iters"])
+        # the CPU arm runs a bounded SAMPLE of the workload named above (same regions, K, basis; fewer cells): say so
+        # where the driver compares configs
+        config = dict(config, sample_cells=n_s, sample_pairs=r["P"], sharding="host cores (%d threads)" % r["cores"])
         print(json.dumps(dict(impl="reference", metric=METRIC, value=r["value"], unit=UNIT, n_gpus=args.gpus,
                               steps=steps, warmup=warmup, ms_per_step=1e3 * r["seconds"] / max(1, r["iters"]),
                               higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f64",
@@ -240,27 +272,39 @@ def main():
     achieved = alg_bytes / (sweep_ms * 1e-3) / 1e9
     value = P_tot * steps / (ms * 1e-3)
     res = eng.fetch()
+    eng_info = eng.layout_info()
     ari = mb.cluster_ari(tr["C_true"], res["r_nk"])
     line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=steps, warmup=warmup,
                 ms_per_step=ms / steps, higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f64",
                 data="synthetic", config=config)
     if rank == 0:
+        # dram__bytes_read + write of one sweep launch from the last `ncu --set full` capture of this kernel
+        # (profiles/sweep_traffic.json names the capture it came from); null when the capture is of another kernel
         traffic = None
         tp = os.path.join(ROOT, "profiles", "sweep_traffic.json")
         if os.path.exists(tp):
-            traffic = json.load(open(tp)).get(args.workload)
+            tj = json.load(open(tp))
+            if tj.get("kernel") == "sweep3_kernel":
+                traffic = tj.get(args.workload)
             if traffic is not None:
                 traffic = traffic / world          # captured on one GPU holding the whole job; a shard moves 1/world of it
-        line["roofline"] = dict(bound="hbm", kernel="sweep_kernel", achieved=achieved, peak=peak, unit="GB/s",
+        line["roofline"] = dict(bound="hbm", kernel="sweep3_kernel", achieved=achieved, peak=peak, unit="GB/s",
                                 frac=achieved / peak, traffic=traffic, peak_source=peak_src,
                                 algorithmic_bytes_per_launch=alg_bytes, kernel_ms=sweep_ms,
                                 whole_step_frac=(algorithmic_bytes(nnz_tot, P_tot, D) / world) / (ms / steps * 1e-3) / 1e9 / peak)
-        # second view of the same kernel: it is FP64-issue bound, not HBM bound.  70 FP64
-        # operations per CpG in the row loop (26 basis, 4 dot, 27 truncated-normal mean, 5 accumulate, 8 misc) plus
-        # 25 K per pair; peak = DFMA rate measured on this pool's B200 with tools/fp64_peak.cu.
-        fp64_ops = 70.0 * nnz_loc + 25.0 * K * P_loc
-        line["fp64"] = dict(achieved=fp64_ops / (sweep_ms * 1e-3) / 1e12, peak=18.1, unit="T FP64 op/s",
-                            frac=fp64_ops / (sweep_ms * 1e-3) / 1e12 / 18.1, ops_per_cpg=70, ops_per_pair=25 * K)
+        # second view of the same kernel: it is FP64-issue bound, not HBM bound.  52 FP64
+        # operations per CpG in the row loop (24 basis, 4 dot, 19 truncated-normal mean, 5 accumulate) plus 30 K per
+        # pair (5 K mean, 20 K E-step terms, 5 K fixed-point conversion); peak = DFMA rate measured on this pool's
+        # B200 with tools/fp64_peak.cu (profiles/fp64_peak.json).
+        fp64_peak, fp64_src = 18.1, "round-1 measurement (profiles/fp64_peak.json missing)"
+        fpp = os.path.join(ROOT, "profiles", "fp64_peak.json")
+        if os.path.exists(fpp):
+            fp64_peak, fp64_src = float(json.load(open(fpp))["dfma_T_per_s"]), "profiles/fp64_peak.json (tools/fp64_peak.cu on this pool)"
+        fp64_ops = 52.0 * nnz_loc + 30.0 * K * P_loc
+        line["fp64"] = dict(achieved=fp64_ops / (sweep_ms * 1e-3) / 1e12, peak=fp64_peak, unit="T FP64 op/s",
+                            frac=fp64_ops / (sweep_ms * 1e-3) / 1e12 / fp64_peak, ops_per_cpg=52, ops_per_pair=30 * K,
+                            peak_source=fp64_src)
+        line["layout"] = eng_info
         line["kernels_ms_per_step"] = {k: v[0] / steps for k, v in prof.items()}
         line["gpu_launches"] = launches
         line["clocks"] = clocks
@@ -325,9 +369,9 @@ def main():
     if rank == 0:
         line["e2e"] = e2e
         if world == 1 and not args.no_cpu:
-            n_s = args.cpu_sample_cells or max(40, min(wl["N"], int(2.0e6 / wl["M"])))
-            d, trs = synth.generate(n_s, wl["M"], K, n_basis=wl["n_basis"], seed=wl["seed"], N_total=n_s)
-            r = cpu_port_run(d.as_dict(), K, trs["basis"], trs["w0"], 10, 0)
+            n_s = args.cpu_sample_cells or default_sample_cells(wl)
+            d, trs = cpu_sample(wl, n_s)
+            r = cpu_port_run(d, K, trs["basis"], trs["w0"], 10, 0)
             if "time_to_converge" in line:      # the same number of iterations on the host cores, from the sampled rate
                 line["time_to_converge"]["cpu_port_seconds_extrapolated"] = \
                     P_tot * line["time_to_converge"]["iterations"] / r["value"]
