@@ -157,7 +157,12 @@ def test_two_shards_on_one_gpu_equal_the_whole(c1):
     np.testing.assert_allclose(W, one["W"], atol=1e-10)
 
 
-def test_melissa_wrapper_default_initialisation(c1):
+def test_melissa_wrapper_default_initialisation(c1, layout):
+    if layout == "flat":
+        # the default initialisation needs the per-pair MLE kernel, which lives on the sliced layout; there is no CPU path
+        with pytest.raises(Exception, match="sliced layout"):
+            mb.melissa(mb.from_dict(c1), K=2, basis=c1["basis"], vb_max_iter=12, vb_init_nstart=2, is_verbose=False, seed=3)
+        return
     with warnings.catch_warnings():
         warnings.simplefilter("ignore")
         out = mb.melissa(mb.to_nested(mb.from_dict(c1)), K=2, basis=c1["basis"], vb_max_iter=60,
