@@ -27,6 +27,7 @@
 #include "fx128.cuh"
 
 #include <cuda_runtime.h>
+#include <cub/cub.cuh>
 
 #include <algorithm>
 #include <cmath>
@@ -686,6 +687,7 @@ int g_opt_sliced = -1;        // -1 auto, 0 never, 1 require
 int g_opt_sweep_chunk = 0;    // slices per chunk of the sweep, 0 = from the problem size
 int g_opt_sweep_group = 2;    // consecutive slices a warp claims at a time
 int g_opt_sweep_warps = 0;    // warps per CTA of the sweep, 0 = as many as fit
+int g_opt_pack_host = 0;      // 1 = build the slice index with host threads (round 1's builder) instead of on the device
 
 void prof_begin(melissa_handle *h, int id) {
     h->launches++;
@@ -897,19 +899,16 @@ int upload(Tp **dst, const std::vector<Tp> &v) {
 }
 
 // Builds the sliced layout from the host index lists and the device-resident x / y.
-int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair_cell,
-                 const int32_t *pair_region) {
+#include "pack_gpu.cuh"
+
+// The slice index built by host threads from HOST index lists (round 1's builder; the default is the device
+// builder in pack_gpu.cuh, this one stays as its cross-check and for the "pack_host" option).
+int build_slice_index_host(melissa_handle *h, Sliced *sl, const int64_t *pair_ptr, const int32_t *pair_cell,
+                           const int32_t *pair_region, cudaStream_t st, int64_t **d_src_out) {
     const int N = h->N, M = h->M;
     const int64_t P = h->P;
-    Sliced *sl = new Sliced();
-    h->sl = sl;
     StageTimer tm;
-    // Cells per block = the pool in which the pairs of one region are sorted by length before they are cut
-    // into slices: the larger, the less padding.  256 keeps the block's E-step sums (Tn x K x 16 bytes of
-    // shared memory in the sweep) affordable up to K ~ 24; beyond that the sweep runs with fewer warps.
-    sl->Tn = g_opt_cell_block > 0 ? g_opt_cell_block : 256;
     const int Tn = sl->Tn;
-    sl->NB = (N + Tn - 1) / Tn;
     std::vector<int64_t> cell_ptr((size_t)N + 1, 0);
     for (int n = 0; n <= N; ++n)       // pair_cell is sorted: N + 1 binary searches instead of a pass over P
         cell_ptr[(size_t)n] = std::lower_bound(pair_cell, pair_cell + P, (int32_t)n) - pair_cell;
@@ -995,6 +994,80 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
             for (size_t q = 0; q < reg.size(); ++q) reg_slice[(size_t)cur[reg[q]]++] = (int32_t)(soff[(size_t)t] + (int64_t)q);
         }
     }
+    // ---- chunks of the sweep: runs of consecutive slices that stay inside one cell block
+    std::vector<int32_t> chunk_ptr;
+    {
+        // (a chunk adds to a shared accumulator at most once per slice; LIMB_MAX_ADDS is what its limbs can absorb)
+        const int64_t target = std::min<int64_t>(LIMB_MAX_ADDS, g_opt_sweep_chunk > 0
+                                   ? g_opt_sweep_chunk
+                                   : std::max<int64_t>(384, std::min<int64_t>(2048, S / ((int64_t)h->sm_count * 16))));
+        int64_t s0 = 0;
+        for (int t = 0; t < nthr; ++t) {
+            const auto &cbv = parts[(size_t)t].slice_cb;
+            size_t q = 0;
+            while (q < cbv.size()) {
+                size_t e = q;
+                while (e < cbv.size() && cbv[e] == cbv[q]) ++e;          // [q, e): the slices of one cell block
+                const int64_t n = (int64_t)(e - q), pieces = std::max<int64_t>(1, (n + target - 1) / target);
+                for (int64_t c = 0; c < pieces; ++c) chunk_ptr.push_back((int32_t)(s0 + (int64_t)q + n * c / pieces));
+                q = e;
+            }
+            s0 += (int64_t)cbv.size();
+        }
+        chunk_ptr.push_back((int32_t)S);
+        sl->NC = (int)chunk_ptr.size() - 1;
+    }
+    tm.lap("region index");
+    // ---- upload, piece by piece
+    int rc;
+    int64_t *d_src = nullptr;
+    if ((rc = dev_alloc(&sl->slice_xbase, S)) || (rc = dev_alloc(&sl->slice_ybase, S)) ||
+        (rc = dev_alloc(&sl->slice_len, S)) || (rc = dev_alloc(&sl->slice_region, S)) ||
+        (rc = dev_alloc(&sl->slice_cb, S)) || (rc = dev_alloc(&sl->lane_cell, S * 32)) ||
+        (rc = dev_alloc(&sl->lane_meta, S * 32)) || (rc = dev_alloc(&sl->lane_pair, S * 32)) ||
+        (rc = dev_alloc(&d_src, S * 32)) || (rc = upload(&sl->chunk_ptr, chunk_ptr)) ||
+        (rc = upload(&sl->blk_cells, blk_cells)) || (rc = upload(&sl->reg_slice_ptr, reg_slice_ptr)) ||
+        (rc = upload(&sl->reg_slice, reg_slice))) {
+        cudaFree(d_src);
+        return rc;
+    }
+    for (int t = 0; t < nthr; ++t) {
+        const SliceBuild &pt = parts[(size_t)t];
+        const int64_t o = soff[(size_t)t];
+        const size_t n = pt.slice_region.size();
+        if (!n) continue;
+#define PUT(dst, vec, mul, Tp)                                                                              \
+        if (cudaMemcpyAsync(dst + o * mul, vec.data(), n * mul * sizeof(Tp), cudaMemcpyHostToDevice, st) != \
+            cudaSuccess) {                                                                                    \
+            cudaFree(d_src);                                                                                  \
+            return fail(MELISSA_ERR_CUDA, "upload of the slice index failed: %s",                             \
+                        cudaGetErrorString(cudaGetLastError()));                                              \
+        }
+        PUT(sl->slice_xbase, xbase[(size_t)t], 1, int64_t)
+        PUT(sl->slice_ybase, ybase[(size_t)t], 1, int64_t)
+        PUT(sl->slice_len, pt.slice_len, 1, int32_t)
+        PUT(sl->slice_region, pt.slice_region, 1, int32_t)
+        PUT(sl->slice_cb, pt.slice_cb, 1, int32_t)
+        PUT(sl->lane_cell, pt.lane_cell, 32, int32_t)
+        PUT(sl->lane_meta, pt.lane_meta, 32, int32_t)
+        PUT(sl->lane_pair, pt.lane_pair, 32, int32_t)
+        PUT(d_src, pt.lane_src, 32, int64_t)
+#undef PUT
+    }
+    if (cudaStreamSynchronize(st) != cudaSuccess) {            // the host vectors go out of scope
+        cudaFree(d_src);
+        return fail(MELISSA_ERR_CUDA, "upload of the slice index failed: %s", cudaGetErrorString(cudaGetLastError()));
+    }
+    *d_src_out = d_src;
+    tm.lap("upload index arrays");
+    return MELISSA_OK;
+}
+
+// Tables, the re-laid observations and the per-pair H^T H, once the slice index exists (either builder).
+int finish_sliced(melissa_handle *h, Sliced *sl, int64_t *d_src, cudaStream_t st, cudaEvent_t xy_arrived) {
+    const int64_t S = sl->S;
+    StageTimer tm;
+    int rc;
     // ---- RBF table (host exp) and the Mills table (device erfcx)
     const BasisDev &b = h->basis;
     const int nb = b.D - 1;
@@ -1027,67 +1100,7 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
         rt.n_entries = 1;
         rbf_tab.assign(1, make_double2(1.0, 1.0));
     }
-    // ---- chunks of the sweep: runs of consecutive slices that stay inside one cell block
-    std::vector<int32_t> chunk_ptr;
-    {
-        // (a chunk adds to a shared accumulator at most once per slice; LIMB_MAX_ADDS is what its limbs can absorb)
-        const int64_t target = std::min<int64_t>(LIMB_MAX_ADDS, g_opt_sweep_chunk > 0
-                                   ? g_opt_sweep_chunk
-                                   : std::max<int64_t>(384, std::min<int64_t>(2048, S / ((int64_t)h->sm_count * 16))));
-        int64_t s0 = 0;
-        for (int t = 0; t < nthr; ++t) {
-            const auto &cbv = parts[(size_t)t].slice_cb;
-            size_t q = 0;
-            while (q < cbv.size()) {
-                size_t e = q;
-                while (e < cbv.size() && cbv[e] == cbv[q]) ++e;          // [q, e): the slices of one cell block
-                const int64_t n = (int64_t)(e - q), pieces = std::max<int64_t>(1, (n + target - 1) / target);
-                for (int64_t c = 0; c < pieces; ++c) chunk_ptr.push_back((int32_t)(s0 + (int64_t)q + n * c / pieces));
-                q = e;
-            }
-            s0 += (int64_t)cbv.size();
-        }
-        chunk_ptr.push_back((int32_t)S);
-        sl->NC = (int)chunk_ptr.size() - 1;
-    }
-    tm.lap("region index + tables");
-    // ---- upload, piece by piece
-    int rc;
-    int64_t *d_src = nullptr;
-    if ((rc = dev_alloc(&sl->slice_xbase, S)) || (rc = dev_alloc(&sl->slice_ybase, S)) ||
-        (rc = dev_alloc(&sl->slice_len, S)) || (rc = dev_alloc(&sl->slice_region, S)) ||
-        (rc = dev_alloc(&sl->slice_cb, S)) || (rc = dev_alloc(&sl->lane_cell, S * 32)) ||
-        (rc = dev_alloc(&sl->lane_meta, S * 32)) || (rc = dev_alloc(&sl->lane_pair, S * 32)) ||
-        (rc = dev_alloc(&d_src, S * 32)) || (rc = upload(&sl->chunk_ptr, chunk_ptr)) ||
-        (rc = upload(&sl->blk_cells, blk_cells)) || (rc = upload(&sl->reg_slice_ptr, reg_slice_ptr)) ||
-        (rc = upload(&sl->reg_slice, reg_slice)) || (rc = upload(&sl->rbf_tab, rbf_tab))) {
-        cudaFree(d_src);
-        return rc;
-    }
-    for (int t = 0; t < nthr; ++t) {
-        const SliceBuild &pt = parts[(size_t)t];
-        const int64_t o = soff[(size_t)t];
-        const size_t n = pt.slice_region.size();
-        if (!n) continue;
-#define PUT(dst, vec, mul, Tp)                                                                              \
-        if (cudaMemcpyAsync(dst + o * mul, vec.data(), n * mul * sizeof(Tp), cudaMemcpyHostToDevice, nullptr) != \
-            cudaSuccess) {                                                                                    \
-            cudaFree(d_src);                                                                                  \
-            return fail(MELISSA_ERR_CUDA, "upload of the slice index failed: %s",                             \
-                        cudaGetErrorString(cudaGetLastError()));                                              \
-        }
-        PUT(sl->slice_xbase, xbase[(size_t)t], 1, int64_t)
-        PUT(sl->slice_ybase, ybase[(size_t)t], 1, int64_t)
-        PUT(sl->slice_len, pt.slice_len, 1, int32_t)
-        PUT(sl->slice_region, pt.slice_region, 1, int32_t)
-        PUT(sl->slice_cb, pt.slice_cb, 1, int32_t)
-        PUT(sl->lane_cell, pt.lane_cell, 32, int32_t)
-        PUT(sl->lane_meta, pt.lane_meta, 32, int32_t)
-        PUT(sl->lane_pair, pt.lane_pair, 32, int32_t)
-        PUT(d_src, pt.lane_src, 32, int64_t)
-#undef PUT
-    }
-    // + 2 prefetch groups of slack: the sweep reads one group past the end of every slice
+    if ((rc = upload(&sl->rbf_tab, rbf_tab))) { cudaFree(d_src); return rc; }
     // slack: the sweep's x ring reads up to NST groups past the end of a slice
     if ((rc = dev_alloc(&sl->x_sell, sl->x_len + 2 * SWEEP3_NST * SWEEP3_XU * 32)) || (rc = dev_alloc(&sl->ybits, sl->y_len)) ||
         (rc = dev_alloc(&sl->stats, S * h->R * 32)) || (rc = dev_alloc(&sl->mills_tab, MILLS_N)) ||
@@ -1095,22 +1108,22 @@ int build_sliced(melissa_handle *h, const int64_t *pair_ptr, const int32_t *pair
         cudaFree(d_src);
         return rc;
     }
-    cudaMemsetAsync(sl->x_sell + sl->x_len, 0, (size_t)2 * SWEEP3_NST * SWEEP3_XU * 32 * sizeof(double), nullptr);
-    tm.lap("upload index arrays");
+    cudaMemsetAsync(sl->x_sell + sl->x_len, 0, (size_t)2 * SWEEP3_NST * SWEEP3_XU * 32 * sizeof(double), st);
+    CU(cudaStreamWaitEvent(st, xy_arrived, 0));                 // the flat x / y must be on the device from here on
     const int grid = (int)((S * 32 + 255) / 256);
-    sell_fill_kernel<<<grid, 256>>>(h->x, h->y, d_src, sl->lane_meta, sl->slice_xbase, sl->slice_ybase, sl->slice_len,
+    sell_fill_kernel<<<grid, 256, 0, st>>>(h->x, h->y, d_src, sl->lane_meta, sl->slice_xbase, sl->slice_ybase, sl->slice_len,
                                     sl->x_sell, sl->ybits, S);
     {
         auto run = [&]() -> int {
-            DISPATCH_D(h->D, hh_sliced_kernel<DD><<<grid, 256>>>(sl->x_sell, sl->slice_xbase, sl->lane_meta, sl->stats,
+            DISPATCH_D(h->D, hh_sliced_kernel<DD><<<grid, 256, 0, st>>>(sl->x_sell, sl->slice_xbase, sl->lane_meta, sl->stats,
                                                                 S, h->basis));
             return MELISSA_OK;
         };
         if ((rc = run())) { cudaFree(d_src); return rc; }
     }
-    mills_table_kernel<<<(MILLS_N + 255) / 256, 256>>>(sl->mills_tab);
+    mills_table_kernel<<<(MILLS_N + 255) / 256, 256, 0, st>>>(sl->mills_tab);
     h->launches += 3;
-    const cudaError_t e = cudaDeviceSynchronize();
+    const cudaError_t e = cudaStreamSynchronize(st);
     cudaFree(d_src);
     if (e != cudaSuccess) return fail(MELISSA_ERR_CUDA, "sliced layout build failed: %s", cudaGetErrorString(e));
     tm.lap("fill + HtH kernels");
@@ -1386,6 +1399,16 @@ extern "C" {
 const char *melissa_last_error(void) { return g_err.c_str(); }
 int melissa_abi_version(void) { return 1; }
 
+static const char *pair_list_error(int code) {
+    switch (code) {
+        case 1: return "pair %lld: cell/region index out of range";
+        case 2: return "pairs must be cell-major (pair %lld)";
+        case 4: return "regions must be strictly increasing inside a cell (pair %lld)";
+        case 5: return "pair %lld has no CpG";
+        default: return "pair %lld has more than 65535 CpGs";
+    }
+}
+
 static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const int64_t *pair_ptr_in,
                      const int32_t *pair_cell_in, const int32_t *pair_region_in, const double *x,
                      const uint8_t *y, int32_t basis_kind, int32_t n_basis, const double *mus,
@@ -1393,26 +1416,9 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
                      melissa_handle **out) {
     if (!out) return fail(MELISSA_ERR_ARG, "out is NULL");
     StageTimer tm_pack;
-    const int64_t *pair_ptr = pair_ptr_in;
-    const int32_t *pair_cell = pair_cell_in, *pair_region = pair_region_in;
-    std::vector<int64_t> host_ptr;
-    std::vector<int32_t> host_cell, host_region;
-    if (on_device && n_pairs > 0 && pair_ptr_in && pair_cell_in && pair_region_in) {
-        // the index lists are validated and inverted on the host; x / y never leave the device
-        CU(cudaSetDevice(device));
-        host_ptr.resize((size_t)n_pairs + 1);
-        host_cell.resize((size_t)n_pairs);
-        host_region.resize((size_t)n_pairs);
-        CU(cudaMemcpy(host_ptr.data(), pair_ptr_in, host_ptr.size() * sizeof(int64_t), cudaMemcpyDeviceToHost));
-        CU(cudaMemcpy(host_cell.data(), pair_cell_in, host_cell.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
-        CU(cudaMemcpy(host_region.data(), pair_region_in, host_region.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
-        pair_ptr = host_ptr.data();
-        pair_cell = host_cell.data();
-        pair_region = host_region.data();
-    }
     *out = nullptr;
     if (n_cells <= 0 || n_regions <= 0) return fail(MELISSA_ERR_ARG, "N > 0 and M > 0 are required");
-    if (n_pairs <= 0 || !pair_ptr || !pair_cell || !pair_region || !x || !y)
+    if (n_pairs <= 0 || !pair_ptr_in || !pair_cell_in || !pair_region_in || !x || !y)
         return fail(MELISSA_ERR_ARG, "empty or NULL observation arrays");
     if (n_pairs >= (int64_t)std::numeric_limits<int32_t>::max())
         return fail(MELISSA_ERR_ARG, "more than 2^31-1 pairs on one GPU; shard the cells");
@@ -1421,9 +1427,38 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
     if (n_basis < 0 || n_basis + 1 > MAX_D || (n_basis > 0 && !mus))
         return fail(MELISSA_ERR_ARG, "basis$M must be in 0..%d", MAX_D - 1);
     if (!(gamma > 0.0) && n_basis > 0) return fail(MELISSA_ERR_ARG, "basis$gamma must be positive");
-    tm_pack.lap("index lists to host");
-    // ---- validate the pair list (host) and build the region-major index
     const int64_t P = n_pairs;
+    BasisDev basis_chk{};
+    basis_chk.D = n_basis + 1;
+    basis_chk.gamma = gamma;
+    for (int j = 0; j < n_basis && j < MAX_MUS; ++j) basis_chk.mus[j] = mus[j];
+    const bool use_sliced = g_opt_sliced != 0 && rbf_equally_spaced(basis_chk) && rbf_table_log2(basis_chk) >= 0;
+    if (g_opt_sliced == 1 && !use_sliced)
+        return fail(MELISSA_ERR_ARG, "the sliced path needs equally spaced RBF centres (and a gamma its table can resolve)");
+    // Where the layout is built: on the device (default for the sliced layout), or by host threads from host copies
+    // of the index lists (the flat layout's region-major index, and the "pack_host" cross-check).
+    const bool host_build = !use_sliced || g_opt_pack_host != 0;
+    const int64_t *pair_ptr = pair_ptr_in;
+    const int32_t *pair_cell = pair_cell_in, *pair_region = pair_region_in;
+    std::vector<int64_t> host_ptr;
+    std::vector<int32_t> host_cell, host_region;
+    if (on_device && host_build) {
+        CU(cudaSetDevice(device));
+        host_ptr.resize((size_t)P + 1);
+        host_cell.resize((size_t)P);
+        host_region.resize((size_t)P);
+        CU(cudaMemcpy(host_ptr.data(), pair_ptr_in, host_ptr.size() * sizeof(int64_t), cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(host_cell.data(), pair_cell_in, host_cell.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(host_region.data(), pair_region_in, host_region.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
+        pair_ptr = host_ptr.data();
+        pair_cell = host_cell.data();
+        pair_region = host_region.data();
+    }
+    const bool have_host_lists = !on_device || host_build;
+    std::vector<int64_t> reg_cnt((size_t)n_regions + 1, 0);
+    int64_t nnz = 0;
+    if (have_host_lists) {
+    // ---- validate the pair list on the host (before the first CUDA call when the lists are host memory)
     if (pair_ptr[0] != 0) return fail(MELISSA_ERR_ARG, "pair_ptr[0] must be 0");
     std::vector<int64_t> reg_cnt((size_t)n_regions + 1, 0);
     {
@@ -1480,19 +1515,13 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
         for (int t = 0; t < nthr; ++t)
             for (int32_t m = 0; m < n_regions; ++m) reg_cnt[(size_t)m + 1] += cnt[(size_t)t][(size_t)m];
     }
-    const int64_t nnz = pair_ptr[P];
+    nnz = pair_ptr[P];
     if (!allow_empty_regions)
         for (int32_t m = 0; m < n_regions; ++m)
             if (reg_cnt[(size_t)m + 1] == 0)
                 return fail(MELISSA_ERR_ARG, "region %d is not covered by any cell", m);
     for (int32_t m = 0; m < n_regions; ++m) reg_cnt[(size_t)m + 1] += reg_cnt[m];
-    BasisDev basis_chk{};
-    basis_chk.D = n_basis + 1;
-    basis_chk.gamma = gamma;
-    for (int j = 0; j < n_basis && j < MAX_MUS; ++j) basis_chk.mus[j] = mus[j];
-    const bool use_sliced = g_opt_sliced != 0 && rbf_equally_spaced(basis_chk) && rbf_table_log2(basis_chk) >= 0;
-    if (g_opt_sliced == 1 && !use_sliced)
-        return fail(MELISSA_ERR_ARG, "the sliced path needs equally spaced RBF centres (and a gamma its table can resolve)");
+    }
     std::vector<int32_t> reg_pair, reg_cell;
     if (!use_sliced) {
         reg_pair.resize((size_t)P);
@@ -1504,8 +1533,9 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
             reg_cell[(size_t)q] = pair_cell[p];
         }
     }
-    tm_pack.lap("validate");
-    // ---- device side
+    tm_pack.lap("validate (host)");
+    // ---- device side.  Two streams: `sc` carries the uploads (index lists first, then the 9 bytes per CpG of x / y),
+    //      `sm` builds the layout from the index lists while x / y are still on their way.
     CU(cudaSetDevice(device));
     melissa_handle *h = new melissa_handle();
     h->device = device;
@@ -1516,24 +1546,106 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) h->sm_count = prop.multiProcessorCount;
     int rc = MELISSA_OK;
-    unsigned long long *bad_y = nullptr;
-    auto bail = [&](int code) { cudaFree(bad_y); melissa_free(h); return code; };
-#define H2D(dst, src, n, Tp)                                                                          \
-    if (cudaMemcpyAsync(dst, src, (size_t)(n) * sizeof(Tp), cudaMemcpyDefault, nullptr) != cudaSuccess)    \
-        return bail(fail(MELISSA_ERR_CUDA, "copy of " #src " failed: %s", cudaGetErrorString(cudaGetLastError())))
+    unsigned long long *bad_y = nullptr, *first_bad = nullptr;
+    int *reg_seen = nullptr;
+    int64_t *d_ptr = nullptr, *d_src = nullptr;
+    int32_t *d_cell = nullptr, *d_reg = nullptr;
+    cudaStream_t sc = nullptr, sm = nullptr;
+    cudaEvent_t e_idx = nullptr, e_xy = nullptr;
+    auto release = [&]() {
+        cudaFree(bad_y); cudaFree(first_bad); cudaFree(reg_seen); cudaFree(d_src);
+        if (!on_device) { cudaFree(d_ptr); cudaFree(d_cell); cudaFree(d_reg); }
+        if (sc) { cudaStreamSynchronize(sc); cudaStreamDestroy(sc); }
+        if (sm) { cudaStreamSynchronize(sm); cudaStreamDestroy(sm); }
+        if (e_idx) cudaEventDestroy(e_idx);
+        if (e_xy) cudaEventDestroy(e_xy);
+    };
+    auto bail = [&](int code) { release(); melissa_free(h); return code; };
+#define PK(call)                                                                                          \
+    if ((call) != cudaSuccess)                                                                             \
+        return bail(fail(MELISSA_ERR_CUDA, "pack: %s failed: %s", #call, cudaGetErrorString(cudaGetLastError())))
+    PK(cudaStreamCreateWithFlags(&sc, cudaStreamNonBlocking));
+    PK(cudaStreamCreateWithFlags(&sm, cudaStreamNonBlocking));
+    PK(cudaEventCreateWithFlags(&e_idx, cudaEventDisableTiming));
+    PK(cudaEventCreateWithFlags(&e_xy, cudaEventDisableTiming));
+    const bool device_build = use_sliced && !host_build;
+    if (device_build) {
+        if (on_device) {
+            d_ptr = const_cast<int64_t *>(pair_ptr_in); d_cell = const_cast<int32_t *>(pair_cell_in); d_reg = const_cast<int32_t *>(pair_region_in);
+        } else {
+            if ((rc = dev_alloc(&d_ptr, P + 1)) || (rc = dev_alloc(&d_cell, P)) || (rc = dev_alloc(&d_reg, P))) return bail(rc);
+            PK(cudaMemcpyAsync(d_ptr, pair_ptr_in, (size_t)(P + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, sc));
+            PK(cudaMemcpyAsync(d_cell, pair_cell_in, (size_t)P * sizeof(int32_t), cudaMemcpyHostToDevice, sc));
+            PK(cudaMemcpyAsync(d_reg, pair_region_in, (size_t)P * sizeof(int32_t), cudaMemcpyHostToDevice, sc));
+        }
+    }
+    PK(cudaEventRecord(e_idx, sc));
+    if (!have_host_lists) {
+        // lists that live on the device are validated there (same rules, same messages)
+        if ((rc = dev_alloc(&first_bad, 1)) || (rc = dev_alloc(&reg_seen, n_regions))) return bail(rc);
+        PK(cudaMemsetAsync(first_bad, 0xff, sizeof(unsigned long long), sm));
+        PK(cudaMemsetAsync(reg_seen, 0, (size_t)n_regions * sizeof(int), sm));
+        pk_validate_kernel<<<grid_for(P, 256, h->sm_count, 8), 256, 0, sm>>>(d_ptr, d_cell, d_reg, P, n_cells, n_regions, first_bad, reg_seen);
+        unsigned long long fb = 0;
+        int64_t head_tail[2] = {0, 0};
+        int32_t last_cell = 0;
+        std::vector<int> seen((size_t)n_regions);
+        PK(cudaMemcpyAsync(&fb, first_bad, sizeof fb, cudaMemcpyDeviceToHost, sm));
+        PK(cudaMemcpyAsync(&head_tail[0], d_ptr, 8, cudaMemcpyDeviceToHost, sm));
+        PK(cudaMemcpyAsync(&head_tail[1], d_ptr + P, 8, cudaMemcpyDeviceToHost, sm));
+        PK(cudaMemcpyAsync(&last_cell, d_cell + (P - 1), 4, cudaMemcpyDeviceToHost, sm));
+        PK(cudaMemcpyAsync(seen.data(), reg_seen, (size_t)n_regions * sizeof(int), cudaMemcpyDeviceToHost, sm));
+        PK(cudaStreamSynchronize(sm));
+        if (head_tail[0] != 0) return bail(fail(MELISSA_ERR_ARG, "pair_ptr[0] must be 0"));
+        if (fb != ~0ull) {
+            const long long bp = (long long)(fb >> 3);
+            const int code = (int)(fb & 7);
+            if (code == 3) {
+                int32_t prev = -1;
+                if (bp > 0) PK(cudaMemcpy(&prev, d_cell + (bp - 1), 4, cudaMemcpyDeviceToHost));
+                return bail(fail(MELISSA_ERR_ARG, "cell %d: No coverage across all regions. This cell should be discarded!", prev + 1));
+            }
+            return bail(fail(MELISSA_ERR_ARG, pair_list_error(code), bp));
+        }
+        if (last_cell != n_cells - 1)
+            return bail(fail(MELISSA_ERR_ARG, "cell %d: No coverage across all regions. This cell should be discarded!", last_cell + 1));
+        if (!allow_empty_regions)
+            for (int32_t m = 0; m < n_regions; ++m)
+                if (!seen[(size_t)m]) return bail(fail(MELISSA_ERR_ARG, "region %d is not covered by any cell", m));
+        nnz = head_tail[1];
+        h->nnz = nnz;
+        tm_pack.lap("validate (device)");
+    }
     if ((rc = dev_alloc(&h->x, nnz))) return bail(rc);
     if ((rc = dev_alloc(&h->y, nnz))) return bail(rc);
-    H2D(h->x, x, nnz, double);
-    H2D(h->y, y, nnz, uint8_t);
-    // y is checked on the device once it has arrived; the verdict is read after the host has built the
-    // layout, so that (from pinned memory) the copy and the host work overlap
+    PK(cudaMemcpyAsync(h->x, x, (size_t)nnz * sizeof(double), cudaMemcpyDefault, sc));
+    PK(cudaMemcpyAsync(h->y, y, (size_t)nnz * sizeof(uint8_t), cudaMemcpyDefault, sc));
+    // y is checked on the device once it has arrived; the verdict is read at the end
     if ((rc = dev_alloc(&bad_y, 1))) return bail(rc);
-    cudaMemsetAsync(bad_y, 0, sizeof(unsigned long long), nullptr);
-    count_bad_y_kernel<<<grid_for(nnz, 256, h->sm_count, 8), 256>>>(h->y, nnz, bad_y);
-    tm_pack.lap("x / y to device");
+    PK(cudaMemsetAsync(bad_y, 0, sizeof(unsigned long long), sc));
+    count_bad_y_kernel<<<grid_for(nnz, 256, h->sm_count, 8), 256, 0, sc>>>(h->y, nnz, bad_y);
+    PK(cudaEventRecord(e_xy, sc));
+    tm_pack.lap("uploads queued");
     if (use_sliced) {
-        // v2: re-lay the observations into region slices, then drop the flat copies
-        if ((rc = build_sliced(h, pair_ptr, pair_cell, pair_region))) return bail(rc);
+        // re-lay the observations into region slices, then drop the flat copies
+        Sliced *sl = new Sliced();
+        h->sl = sl;
+        // Cells per block = the pool in which the pairs of one region are sorted by length before they are cut
+        // into slices: the larger, the less padding.  256 keeps the block's E-step sums (Tn x K x 16 bytes of
+        // shared memory in the sweep) affordable up to K ~ 24; beyond that the sweep runs with fewer warps.
+        sl->Tn = g_opt_cell_block > 0 ? g_opt_cell_block : 256;
+        sl->NB = (n_cells + sl->Tn - 1) / sl->Tn;
+        if (device_build) {
+            PK(cudaStreamWaitEvent(sm, e_idx, 0));
+            if ((rc = build_slice_index_device(h, sl, d_ptr, d_cell, d_reg, sm, &d_src, g_opt_sweep_chunk))) return bail(rc);
+        } else {
+            if ((rc = build_slice_index_host(h, sl, pair_ptr, pair_cell, pair_region, sm, &d_src))) return bail(rc);
+        }
+        tm_pack.lap("slice index");
+        rc = finish_sliced(h, sl, d_src, sm, e_xy);
+        d_src = nullptr;                       // freed by finish_sliced
+        if (rc) return bail(rc);
+        tm_pack.lap("tables, fill, H^T H");
         cudaFree(h->x); cudaFree(h->y);
         h->x = nullptr; h->y = nullptr;
     } else {
@@ -1544,31 +1656,29 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
         if ((rc = dev_alloc(&h->reg_pair, P))) return bail(rc);
         if ((rc = dev_alloc(&h->reg_cell, P))) return bail(rc);
         if ((rc = dev_alloc(&h->stats, P * h->R))) return bail(rc);
-        H2D(h->pair_ptr, pair_ptr_in, P + 1, int64_t);
-        H2D(h->pair_cell, pair_cell_in, P, int32_t);
-        H2D(h->pair_region, pair_region_in, P, int32_t);
-        H2D(h->reg_ptr, reg_cnt.data(), n_regions + 1, int64_t);
-        H2D(h->reg_pair, reg_pair.data(), P, int32_t);
-        H2D(h->reg_cell, reg_cell.data(), P, int32_t);
+        PK(cudaMemcpyAsync(h->pair_ptr, pair_ptr_in, (size_t)(P + 1) * sizeof(int64_t), cudaMemcpyDefault, sc));
+        PK(cudaMemcpyAsync(h->pair_cell, pair_cell_in, (size_t)P * sizeof(int32_t), cudaMemcpyDefault, sc));
+        PK(cudaMemcpyAsync(h->pair_region, pair_region_in, (size_t)P * sizeof(int32_t), cudaMemcpyDefault, sc));
+        PK(cudaMemcpyAsync(h->reg_ptr, reg_cnt.data(), (size_t)(n_regions + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, sc));
+        PK(cudaMemcpyAsync(h->reg_pair, reg_pair.data(), (size_t)P * sizeof(int32_t), cudaMemcpyHostToDevice, sc));
+        PK(cudaMemcpyAsync(h->reg_cell, reg_cell.data(), (size_t)P * sizeof(int32_t), cudaMemcpyHostToDevice, sc));
         const int grid = grid_for(P, 128, h->sm_count, 16);
         auto run = [&]() -> int {
-            DISPATCH_D(h->D, hh_kernel<DD><<<grid, 128>>>(h->pair_ptr, h->x, h->stats, P, h->basis));
+            DISPATCH_D(h->D, hh_kernel<DD><<<grid, 128, 0, sc>>>(h->pair_ptr, h->x, h->stats, P, h->basis));
             return MELISSA_OK;
         };
         if ((rc = run())) return bail(rc);
         h->launches++;
     }
-#undef H2D
     {
         unsigned long long bad_h = 0;
-        const cudaError_t e = cudaMemcpy(&bad_h, bad_y, sizeof bad_h, cudaMemcpyDeviceToHost);
-        cudaFree(bad_y);
-        bad_y = nullptr;
-        if (e != cudaSuccess) return bail(fail(MELISSA_ERR_CUDA, "pack failed: %s", cudaGetErrorString(e)));
+        PK(cudaMemcpyAsync(&bad_h, bad_y, sizeof bad_h, cudaMemcpyDeviceToHost, sc));
+        PK(cudaStreamSynchronize(sc));
         if (bad_h) return bail(fail(MELISSA_ERR_ARG, "%llu methylation states are not 0/1", bad_h));
     }
-    if (cudaDeviceSynchronize() != cudaSuccess)
-        return bail(fail(MELISSA_ERR_CUDA, "pack failed: %s", cudaGetErrorString(cudaGetLastError())));
+    PK(cudaStreamSynchronize(sm));
+#undef PK
+    release();
     *out = h;
     return MELISSA_OK;
 }
@@ -1634,6 +1744,10 @@ int melissa_set_option(const char *key, int64_t value) {
         return MELISSA_OK;
     }
     if (!std::strcmp(key, "clusters_hint")) return MELISSA_OK;      // round-1 knob: the layout no longer depends on K
+    if (!std::strcmp(key, "pack_host")) {
+        g_opt_pack_host = value != 0;
+        return MELISSA_OK;
+    }
     if (!std::strcmp(key, "debug_estep")) {
         g_opt_debug_estep = value != 0;
         return MELISSA_OK;

@@ -75,3 +75,44 @@ def test_alpha_of_the_bundled_synthetic_fit_is_below_61(c1):
     with mb.Engine(mb.from_dict(c1), c1["basis"]) as eng:
         res = eng.run(2, c1["w0_k2"], c1["k2_delta_0"], vb_max_iter=10)
     assert np.all(res["alpha"] < 61) and np.all(res["alpha"] == 60.5)
+
+
+def test_device_built_layout_equals_the_host_built_one(c1):
+    """melissa_pack builds the slice index on the device (radix sorts and scans, pack_gpu.cuh); round 1's host-thread
+    builder stays behind the "pack_host" option.  Same slices in the same order, so the fit must agree to the last bit."""
+    K = 5
+    d, tr = synth.generate(300, 64, K, n_basis=4, seed=9, sites_per_region=60, cov_lo=0.02, cov_hi=0.3)
+    delta_0 = np.full(K, 0.55)
+    out = {}
+    for host in (0, 1):
+        mb.set_option("pack_host", host)
+        try:
+            with mb.Engine(d, tr["basis"]) as eng:
+                out[host] = (eng.layout_info(), eng.run(K, tr["w0"], delta_0, vb_max_iter=20))
+        finally:
+            mb.set_option("pack_host", 0)
+    assert out[0][0] == out[1][0]
+    assert np.array_equal(out[0][1]["lb"], out[1][1]["lb"])
+    assert np.array_equal(out[0][1]["r_nk"], out[1][1]["r_nk"])
+    assert np.array_equal(out[0][1]["W"], out[1][1]["W"])
+
+
+def test_device_resident_index_lists_are_validated_on_the_device():
+    """melissa_pack_device checks the pair list with a kernel: same rules and messages as the host check."""
+    import torch
+    K = 2
+    dev, tr = synth.generate_device(64, 20, K, n_basis=3, seed=4, chunk_cells=32)
+    bad = dict(dev)
+    pc = dev["pair_cell"].clone()
+    pc[pc == 5] = 6                                            # cell 5 loses all its regions
+    bad["pair_cell"] = pc
+    with pytest.raises(mb._lib.MelissaError, match="cell 5: No coverage across all regions"):
+        mb.Engine(bad, tr["basis"])
+    bad = dict(dev)
+    pr = dev["pair_region"].clone()
+    pr[3] = pr[2]                                              # not strictly increasing inside a cell
+    bad["pair_region"] = pr
+    with pytest.raises(mb._lib.MelissaError, match="strictly increasing"):
+        mb.Engine(bad, tr["basis"])
+    with mb.Engine(dev, tr["basis"]) as eng:                   # and the untouched lists pack
+        assert eng.layout_info()["pairs"] == int(dev["pair_cell"].shape[0])
