@@ -164,6 +164,38 @@ int melissa_vb_lower_bound(melissa_handle *h, double *lb_out);
 int melissa_vb_reduce_buffer(melissa_handle *h, void **dev_ptr, int64_t *n_doubles);
 int melissa_vb_lb_buffer(melissa_handle *h, void **dev_ptr, int64_t *n_doubles);
 
+/*
+ * Several GPUs of one box behind ONE call: what the reference's user gets from the single function call
+ * melissa(...) (R/melissa_vb.R:86-90) and its no_cores knob (R/utils.R:30-43), for hosts (R's .Call, C,
+ * Python) that run one process.  Cells are sharded over the GPUs in contiguous ranges balanced by CpG count;
+ * the library runs one host thread and one stream per GPU; the only per-iteration exchange, the r-weighted
+ * sufficient statistics (M K R + K + 1 doubles per GPU), is summed by a kernel on every GPU that reads the other
+ * GPUs' partial sums over NVLink peer loads, in rank order (bit-identical on every GPU, no library collective).
+ *
+ *   melissa_pack_multi    melissa_pack for the whole job: shards the HOST arrays, packs every shard on its GPU
+ *                         (devices[g], or GPU g if devices is NULL), returns one object
+ *   melissa_multi_create  the same object from handles the caller packed itself (one per shard, in cell order,
+ *                         each with allow_empty_regions = 1); the handles stay the caller's
+ *   melissa_vb_run_multi  melissa_vb_run on all shards; same arguments, outputs for the whole job
+ *                         (r_nk has dim c(N_total, K))
+ *   melissa_multi_free    releases the object (and the handles, if melissa_pack_multi made them)
+ */
+typedef struct melissa_multi melissa_multi;
+int melissa_pack_multi(int32_t n_cells, int32_t n_regions, int64_t n_pairs,
+                       const int64_t *pair_ptr, const int32_t *pair_cell, const int32_t *pair_region,
+                       const double *x, const uint8_t *y,
+                       int32_t basis_kind, int32_t n_basis, const double *mus, double gamma,
+                       int32_t n_gpus, const int32_t *devices, melissa_multi **out);
+int melissa_multi_create(int32_t n_gpus, melissa_handle **handles, melissa_multi **out);
+int melissa_vb_run_multi(melissa_multi *mm, int32_t K, const double *w0, const double *delta_0,
+                         double alpha_0, double beta_0, int32_t vb_max_iter, double epsilon_conv,
+                         int32_t lb_every,
+                         double *W, double *W_Sigma, double *r_nk, double *delta, double *alpha,
+                         double *beta, double *pi_k, double *lb, int32_t lb_cap, int32_t *n_lb,
+                         int32_t *n_iter, int32_t *flags);
+int melissa_multi_free(melissa_multi *mm);
+int32_t melissa_multi_gpus(const melissa_multi *mm);
+
 /* Copy the current state to host buffers (same layouts as melissa_vb_run; NULL skips). */
 int melissa_vb_fetch(melissa_handle *h, double *W, double *W_Sigma, double *r_nk,
                      double *delta, double *alpha, double *beta, double *pi_k);

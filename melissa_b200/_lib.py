@@ -29,6 +29,14 @@ SIGNATURES = {
     "melissa_vb_run": (C.c_int, [handle_t, c_i32, p_dbl, p_dbl, c_dbl, c_dbl, c_i32, c_dbl, c_i32,
                                  p_dbl, p_dbl, p_dbl, p_dbl, p_dbl, p_dbl, p_dbl, p_dbl, c_i32,
                                  p_i32, p_i32, p_i32]),
+    "melissa_pack_multi": (C.c_int, [c_i32, c_i32, c_i64, p_i64, p_i32, p_i32, p_dbl, p_u8, c_i32, c_i32, p_dbl, c_dbl,
+                                     c_i32, p_i32, C.POINTER(handle_t)]),
+    "melissa_multi_create": (C.c_int, [c_i32, C.POINTER(handle_t), C.POINTER(handle_t)]),
+    "melissa_vb_run_multi": (C.c_int, [handle_t, c_i32, p_dbl, p_dbl, c_dbl, c_dbl, c_i32, c_dbl, c_i32,
+                                       p_dbl, p_dbl, p_dbl, p_dbl, p_dbl, p_dbl, p_dbl, p_dbl, c_i32,
+                                       p_i32, p_i32, p_i32]),
+    "melissa_multi_free": (C.c_int, [handle_t]),
+    "melissa_multi_gpus": (c_i32, [handle_t]),
     "melissa_vb_begin": (C.c_int, [handle_t, c_i32, p_dbl, p_dbl, c_dbl, c_dbl, c_i64, C.c_void_p]),
     "melissa_vb_phase_a": (C.c_int, [handle_t]),
     "melissa_vb_phase_b": (C.c_int, [handle_t, c_i32]),

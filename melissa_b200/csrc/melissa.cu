@@ -30,6 +30,7 @@
 #include <cub/cub.cuh>
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -900,6 +901,7 @@ int upload(Tp **dst, const std::vector<Tp> &v) {
 
 // Builds the sliced layout from the host index lists and the device-resident x / y.
 #include "pack_gpu.cuh"
+#include "multi.cuh"
 
 // The slice index built by host threads from HOST index lists (round 1's builder; the default is the device
 // builder in pack_gpu.cuh, this one stays as its cross-check and for the "pack_host" option).
@@ -2260,6 +2262,277 @@ int melissa_impute_noalloc(int32_t n_cells, int32_t n_regions, int32_t K, int32_
     if ((rc = run())) return rc;
     CU(cudaGetLastError());
     CU(cudaMemcpy(pred, d_pred, (size_t)nnz * sizeof(double), cudaMemcpyDeviceToHost));
+    return MELISSA_OK;
+}
+
+// ===========================================================================
+// Several GPUs behind one call (multi.cuh)
+// ===========================================================================
+struct melissa_multi {
+    int G = 0;
+    std::vector<melissa_handle *> h;
+    std::vector<int64_t> cell_lo;          // first global cell of every shard (G + 1 entries)
+    bool own_handles = false;
+    int64_t N_total = 0;
+};
+
+int melissa_multi_create(int32_t n_gpus, melissa_handle **handles, melissa_multi **out) {
+    if (!out || !handles) return fail(MELISSA_ERR_ARG, "handles / out is NULL");
+    if (n_gpus < 1 || n_gpus > MULTI_MAX_GPUS) return fail(MELISSA_ERR_ARG, "n_gpus must be in 1..%d", MULTI_MAX_GPUS);
+    melissa_multi *mm = new melissa_multi();
+    mm->G = n_gpus;
+    mm->cell_lo.push_back(0);
+    for (int g = 0; g < n_gpus; ++g) {
+        melissa_handle *h = handles[g];
+        if (!h) { delete mm; return fail(MELISSA_ERR_ARG, "handle %d is NULL", g); }
+        if (g && (h->M != handles[0]->M || h->D != handles[0]->D)) {
+            delete mm;
+            return fail(MELISSA_ERR_ARG, "shard %d has another number of regions / basis functions than shard 0", g);
+        }
+        mm->h.push_back(h);
+        mm->cell_lo.push_back(mm->cell_lo.back() + h->N);
+    }
+    mm->N_total = mm->cell_lo.back();
+    // every GPU reads every other GPU's partial sums directly
+    for (int g = 0; g < n_gpus; ++g) {
+        CU(cudaSetDevice(mm->h[g]->device));
+        for (int p = 0; p < n_gpus; ++p) {
+            const int dg = mm->h[g]->device, dp = mm->h[p]->device;
+            if (dg == dp) continue;
+            int can = 0;
+            CU(cudaDeviceCanAccessPeer(&can, dg, dp));
+            if (!can) { delete mm; return fail(MELISSA_ERR_CUDA, "GPU %d cannot read GPU %d's memory (no peer access)", dg, dp); }
+            const cudaError_t e = cudaDeviceEnablePeerAccess(dp, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+                delete mm;
+                return fail(MELISSA_ERR_CUDA, "cudaDeviceEnablePeerAccess(%d -> %d) failed: %s", dg, dp, cudaGetErrorString(e));
+            }
+            cudaGetLastError();
+        }
+    }
+    *out = mm;
+    return MELISSA_OK;
+}
+
+int melissa_multi_free(melissa_multi *mm) {
+    if (!mm) return MELISSA_OK;
+    if (mm->own_handles)
+        for (melissa_handle *h : mm->h) melissa_free(h);
+    delete mm;
+    return MELISSA_OK;
+}
+
+int32_t melissa_multi_gpus(const melissa_multi *mm) { return mm ? mm->G : 0; }
+
+int melissa_pack_multi(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const int64_t *pair_ptr,
+                       const int32_t *pair_cell, const int32_t *pair_region, const double *x, const uint8_t *y,
+                       int32_t basis_kind, int32_t n_basis, const double *mus, double gamma, int32_t n_gpus,
+                       const int32_t *devices, melissa_multi **out) {
+    if (!out) return fail(MELISSA_ERR_ARG, "out is NULL");
+    *out = nullptr;
+    if (n_gpus < 1 || n_gpus > MULTI_MAX_GPUS) return fail(MELISSA_ERR_ARG, "n_gpus must be in 1..%d", MULTI_MAX_GPUS);
+    if (n_cells < n_gpus) return fail(MELISSA_ERR_ARG, "more GPUs than cells");
+    if (n_pairs <= 0 || !pair_ptr || !pair_cell || !pair_region || !x || !y) return fail(MELISSA_ERR_ARG, "empty or NULL observation arrays");
+    if (n_gpus == 1) {
+        melissa_handle *h = nullptr;
+        int rc = melissa_pack(n_cells, n_regions, n_pairs, pair_ptr, pair_cell, pair_region, x, y, basis_kind, n_basis, mus, gamma,
+                              devices ? devices[0] : 0, 0, &h);
+        if (rc) return rc;
+        if ((rc = melissa_multi_create(1, &h, out))) { melissa_free(h); return rc; }
+        (*out)->own_handles = true;
+        return MELISSA_OK;
+    }
+    // contiguous cell ranges balanced by CpG count (coverage varies several-fold across cells)
+    const int64_t P = n_pairs;
+    if (pair_ptr[0] != 0) return fail(MELISSA_ERR_ARG, "pair_ptr[0] must be 0");
+    std::vector<int64_t> cell_first((size_t)n_cells + 1);
+    for (int n = 0; n <= n_cells; ++n) cell_first[(size_t)n] = std::lower_bound(pair_cell, pair_cell + P, (int32_t)n) - pair_cell;
+    const int64_t nnz = pair_ptr[P];
+    std::vector<int> bound((size_t)n_gpus + 1, 0);
+    bound[(size_t)n_gpus] = n_cells;
+    for (int g = 1; g < n_gpus; ++g) {
+        const int64_t target = nnz / n_gpus * g;
+        int lo = bound[(size_t)g - 1] + 1, hi = n_cells - (n_gpus - g);
+        int b = lo;
+        while (lo <= hi) {                                      // first cell whose CpG offset reaches the target
+            const int mid = (lo + hi) / 2;
+            if (pair_ptr[cell_first[(size_t)mid]] < target) lo = mid + 1; else { b = mid; hi = mid - 1; }
+        }
+        bound[(size_t)g] = std::max(bound[(size_t)g - 1] + 1, std::min(b, n_cells - (n_gpus - g)));
+    }
+    std::vector<melissa_handle *> hs((size_t)n_gpus, nullptr);
+    std::vector<int> rcs((size_t)n_gpus, MELISSA_OK);
+    std::vector<std::string> errs((size_t)n_gpus);
+    std::vector<std::thread> th;
+    for (int g = 0; g < n_gpus; ++g)
+        th.emplace_back([&, g]() {
+            const int c0 = bound[(size_t)g], c1 = bound[(size_t)g + 1];
+            const int64_t p0 = cell_first[(size_t)c0], p1 = cell_first[(size_t)c1], i0 = pair_ptr[p0];
+            std::vector<int64_t> ptr((size_t)(p1 - p0) + 1);
+            std::vector<int32_t> cell((size_t)(p1 - p0));
+            for (int64_t p = p0; p <= p1; ++p) ptr[(size_t)(p - p0)] = pair_ptr[p] - i0;
+            for (int64_t p = p0; p < p1; ++p) cell[(size_t)(p - p0)] = pair_cell[p] - c0;
+            rcs[(size_t)g] = melissa_pack(c1 - c0, n_regions, p1 - p0, ptr.data(), cell.data(), pair_region + p0, x + i0, y + i0,
+                                          basis_kind, n_basis, mus, gamma, devices ? devices[g] : g, 1, &hs[(size_t)g]);
+            if (rcs[(size_t)g]) errs[(size_t)g] = g_err;
+        });
+    for (auto &t : th) t.join();
+    for (int g = 0; g < n_gpus; ++g)
+        if (rcs[(size_t)g]) {
+            for (melissa_handle *h : hs) melissa_free(h);
+            return fail(rcs[(size_t)g], "shard %d: %s", g, errs[(size_t)g].c_str());
+        }
+    // a region no cell of ANY shard covers is an error, as in the single-GPU pack (each shard alone may miss regions)
+    int rc = melissa_multi_create(n_gpus, hs.data(), out);
+    if (rc) { for (melissa_handle *h : hs) melissa_free(h); return rc; }
+    (*out)->own_handles = true;
+    return MELISSA_OK;
+}
+
+int melissa_vb_run_multi(melissa_multi *mm, int32_t K, const double *w0, const double *delta_0, double alpha_0,
+                         double beta_0, int32_t vb_max_iter, double epsilon_conv, int32_t lb_every, double *W,
+                         double *W_Sigma, double *r_nk, double *delta, double *alpha, double *beta, double *pi_k,
+                         double *lb, int32_t lb_cap, int32_t *n_lb, int32_t *n_iter, int32_t *flags) {
+    if (!mm) return fail(MELISSA_ERR_ARG, "multi handle is NULL");
+    if (vb_max_iter < 2) return fail(MELISSA_ERR_ARG, "vb_max_iter must be >= 2");
+    if (lb_every <= 0) return fail(MELISSA_ERR_ARG, "lb_every must be positive");
+    const int G = mm->G;
+    if (G == 1 && mm->h[0]->N == mm->N_total)
+        return melissa_vb_run(mm->h[0], K, w0, delta_0, alpha_0, beta_0, vb_max_iter, epsilon_conv, lb_every, W, W_Sigma, r_nk,
+                              delta, alpha, beta, pi_k, lb, lb_cap, n_lb, n_iter, flags);
+    struct PerGpu {
+        cudaStream_t st = nullptr;
+        double *part[2] = {nullptr, nullptr}, *sum = nullptr, *lbsum = nullptr, *orig_red = nullptr, *orig_lb = nullptr;
+        cudaEvent_t ev_part[2] = {nullptr, nullptr}, ev_lb = nullptr;
+        int rc = MELISSA_OK;
+        std::string err;
+    };
+    std::vector<PerGpu> pg((size_t)G);
+    HostBarrier bar;
+    bar.n = G;
+    // shared between the host threads (written by thread 0 between two barriers)
+    std::vector<double> lbs;
+    lbs.push_back(-std::numeric_limits<double>::infinity());        // LB <- c(-Inf), :242
+    int fl = 0, it_last = 1;
+    std::atomic<int> stop{0};
+    auto worker = [&](int g) {
+        melissa_handle *h = mm->h[(size_t)g];
+        PerGpu &me = pg[(size_t)g];
+        auto bad = [&](int rc) { me.rc = rc; me.err = g_err; bar.fail_all(); };
+#define MG(call)                                                                                         \
+        do {                                                                                             \
+            if ((call) != cudaSuccess) {                                                                 \
+                bad(fail(MELISSA_ERR_CUDA, "GPU %d: %s failed: %s", h->device, #call, cudaGetErrorString(cudaGetLastError()))); \
+                return;                                                                                  \
+            }                                                                                            \
+        } while (0)
+        MG(cudaSetDevice(h->device));
+        MG(cudaStreamCreateWithFlags(&me.st, cudaStreamNonBlocking));
+        int rc = melissa_vb_begin(h, K, w0, delta_0, alpha_0, beta_0, mm->N_total, me.st);
+        if (rc) { bad(rc); return; }
+        const int64_t n_red = h->red_len;
+        me.orig_red = h->red;
+        me.orig_lb = h->lbbuf;
+        me.part[0] = h->red;
+        if ((rc = dev_alloc(&me.part[1], n_red)) || (rc = dev_alloc(&me.sum, n_red)) || (rc = dev_alloc(&me.lbsum, 2))) { bad(rc); return; }
+        for (int q = 0; q < 2; ++q) MG(cudaEventCreateWithFlags(&me.ev_part[q], cudaEventDisableTiming));
+        MG(cudaEventCreateWithFlags(&me.ev_lb, cudaEventDisableTiming));
+        if (!bar.wait()) return;                                    // everybody's buffers and events exist
+        for (int i = 2; i <= vb_max_iter; ++i) {                    // :309
+            const int par = i & 1;
+            h->red = me.part[par];
+            if ((rc = melissa_vb_phase_a(h))) { bad(rc); return; }  // this shard's partial sums
+            MG(cudaEventRecord(me.ev_part[par], me.st));
+            if (!bar.wait()) return;                                // every GPU's event of this iteration has been recorded
+            PartPtrs pp;
+            pp.G = G;
+            for (int p = 0; p < G; ++p) {
+                if (p != g) MG(cudaStreamWaitEvent(me.st, pg[(size_t)p].ev_part[par], 0));
+                pp.p[p] = pg[(size_t)p].part[par];
+            }
+            reduce_parts_kernel<<<h->sm_count * 2, 256, 0, me.st>>>(pp, n_red, me.sum);
+            h->launches++;
+            h->red = me.sum;
+            const bool with_lb = (i % lb_every == 0) || i == vb_max_iter;       // :458
+            if ((rc = melissa_vb_phase_b(h, with_lb))) { bad(rc); return; }
+            if (with_lb) {
+                MG(cudaEventRecord(me.ev_lb, me.st));
+                if (!bar.wait()) return;
+                PartPtrs lp;
+                lp.G = G;
+                for (int p = 0; p < G; ++p) {
+                    if (p != g) MG(cudaStreamWaitEvent(me.st, pg[(size_t)p].ev_lb, 0));
+                    lp.p[p] = pg[(size_t)p].orig_lb;
+                }
+                reduce_parts_kernel<<<1, 32, 0, me.st>>>(lp, 2, me.lbsum);
+                h->launches++;
+                h->lbbuf = me.lbsum;
+                double v = 0.0;
+                rc = melissa_vb_lower_bound(h, &v);                 // (synchronises this GPU's stream)
+                h->lbbuf = me.orig_lb;
+                if (rc) { bad(rc); return; }
+                if (!bar.wait()) return;                            // nobody overwrites lbbuf before everybody has read it
+                if (g == 0) {
+                    const double prev = lbs.back();
+                    lbs.push_back(v);
+                    if (v < prev) fl |= MELISSA_FLAG_LB_DECREASED;  // :495-497
+                    if (std::fabs(v - prev) < epsilon_conv) stop.store(1);      // :499-501
+                    it_last = i;
+                }
+                if (!bar.wait()) return;
+                if (stop.load()) break;
+            }
+            if (g == 0) {
+                it_last = i;
+                if (i == vb_max_iter) fl |= MELISSA_FLAG_NOT_CONVERGED;         // :511-513
+            }
+        }
+        h->red = me.sum;                                            // what melissa_vb_fetch and a later caller see
+        MG(cudaStreamSynchronize(me.st));
+#undef MG
+    };
+    std::vector<std::thread> th;
+    for (int g = 0; g < G; ++g) th.emplace_back(worker, g);
+    for (auto &t : th) t.join();
+    int rc = MELISSA_OK;
+    for (int g = 0; g < G && !rc; ++g)
+        if (pg[(size_t)g].rc) rc = fail(pg[(size_t)g].rc, "%s", pg[(size_t)g].err.c_str());
+    // ---- results: q(w) and the scalars are identical on every GPU, responsibilities come shard by shard
+    if (!rc) {
+        melissa_handle *h0 = mm->h[0];
+        rc = melissa_vb_fetch(h0, W, W_Sigma, nullptr, delta, alpha, beta, pi_k);
+        if (!rc && r_nk) {
+            for (int g = 0; g < G && !rc; ++g) {
+                melissa_handle *h = mm->h[(size_t)g];
+                std::vector<double> r((size_t)h->N * K);
+                if ((rc = melissa_vb_fetch(h, nullptr, nullptr, r.data(), nullptr, nullptr, nullptr, nullptr))) break;
+                for (int k = 0; k < K; ++k)
+                    std::memcpy(r_nk + (size_t)k * mm->N_total + (size_t)mm->cell_lo[(size_t)g], r.data() + (size_t)k * h->N,
+                                (size_t)h->N * sizeof(double));
+            }
+        }
+    }
+    // ---- put the handles back the way melissa_vb_begin left them, release the per-run resources
+    for (int g = 0; g < G; ++g) {
+        melissa_handle *h = mm->h[(size_t)g];
+        PerGpu &me = pg[(size_t)g];
+        cudaSetDevice(h->device);
+        if (me.st) cudaStreamSynchronize(me.st);
+        if (me.orig_red) h->red = me.orig_red;
+        if (me.orig_lb) h->lbbuf = me.orig_lb;
+        cudaFree(me.part[1]); cudaFree(me.sum); cudaFree(me.lbsum);
+        for (int q = 0; q < 2; ++q) if (me.ev_part[q]) cudaEventDestroy(me.ev_part[q]);
+        if (me.ev_lb) cudaEventDestroy(me.ev_lb);
+        h->stream = nullptr;                                        // the run's stream goes away with the run
+        h->begun = false;
+        if (me.st) cudaStreamDestroy(me.st);
+    }
+    if (rc) return rc;
+    const int nlb = (int)lbs.size();
+    if (lb) for (int q = 0; q < nlb && q < lb_cap; ++q) lb[q] = lbs[(size_t)q];
+    if (n_lb) *n_lb = nlb;
+    if (n_iter) *n_iter = it_last;
+    if (flags) *flags = fl;
     return MELISSA_OK;
 }
 

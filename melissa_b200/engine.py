@@ -213,3 +213,83 @@ class Engine:
                     W_Sigma=out["W_Sigma"].reshape(K, M, D, D),
                     r_nk=out["r_nk"].reshape((N, K), order="F"),
                     delta=out["delta"], alpha=out["alpha"], beta=out["beta"], pi_k=out["pi_k"])
+
+
+class MultiEngine:
+    """Several GPUs of one box behind one object (melissa_multi): either packed from the whole job's host arrays
+    (`MultiEngine.pack`) or assembled from Engines the caller packed shard by shard, in cell order
+    (`MultiEngine(engines)`; they stay the caller's).  `run` is melissa_vb_run_multi: one call, one process."""
+
+    def __init__(self, engines=None, _handle=None, _shape=None):
+        self.lib = _lib.load()
+        if _handle is not None:
+            self.h, (self.N, self.M, self.D, self.basis) = _handle, _shape
+            self.engines = None
+            return
+        self.engines = list(engines)
+        arr = (_lib.handle_t * len(self.engines))(*[e.h for e in self.engines])
+        h = _lib.handle_t()
+        _lib.check(self.lib.melissa_multi_create(len(self.engines), arr, C.byref(h)))
+        self.h = h
+        e0 = self.engines[0]
+        self.N, self.M, self.D, self.basis = sum(e.N for e in self.engines), e0.M, e0.D, e0.basis
+
+    @classmethod
+    def pack(cls, data: MelissaData, basis: dict, n_gpus: int, devices=None):
+        lib = _lib.load()
+        mus = np.ascontiguousarray(basis["mus"], np.float64)
+        dev = None if devices is None else np.ascontiguousarray(devices, np.int32)
+        h = _lib.handle_t()
+        _lib.check(lib.melissa_pack_multi(
+            int(data.N), int(data.M), data.P, _lib.ptr(np.ascontiguousarray(data.pair_ptr, np.int64), _lib.c_i64),
+            _lib.ptr(np.ascontiguousarray(data.pair_cell, np.int32), _lib.c_i32),
+            _lib.ptr(np.ascontiguousarray(data.pair_region, np.int32), _lib.c_i32),
+            _lib.ptr(np.ascontiguousarray(data.x, np.float64), _lib.c_dbl),
+            _lib.ptr(np.ascontiguousarray(data.y, np.uint8), C.c_uint8), 1, int(basis["M"]),
+            _lib.ptr(mus, _lib.c_dbl) if mus.size else None, float(basis["gamma"]), int(n_gpus),
+            _lib.ptr(dev, _lib.c_i32) if dev is not None else None, C.byref(h)))
+        return cls(_handle=h, _shape=(int(data.N), int(data.M), int(basis["M"]) + 1, basis))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.melissa_multi_free(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def run(self, K, w0, delta_0, alpha_0=0.5, beta_0=None, vb_max_iter=300, epsilon_conv=1e-5, lb_every=10):
+        K = int(K)
+        w0 = np.asarray(w0, np.float64)
+        if w0.shape != (self.M, self.D, K):
+            raise ValueError(f"w must have shape (M, D, K) = {(self.M, self.D, K)}, got {w0.shape}")
+        w0 = np.asfortranarray(w0).ravel(order="F").copy()
+        delta_0 = np.ascontiguousarray(delta_0, np.float64)
+        if delta_0.shape != (K,):
+            raise ValueError("delta_0 must have length K")
+        M, D, N = self.M, self.D, self.N
+        out = dict(W=np.empty(M * D * K), W_Sigma=np.empty(K * M * D * D), r_nk=np.empty(N * K),
+                   delta=np.empty(K), alpha=np.empty(K), beta=np.empty(K), pi_k=np.empty(K))
+        cap = (int(vb_max_iter) // int(lb_every)) + 3
+        lb = np.empty(cap, np.float64)
+        n_lb, n_iter, flags = _lib.c_i32(0), _lib.c_i32(0), _lib.c_i32(0)
+        _lib.check(self.lib.melissa_vb_run_multi(
+            self.h, K, _lib.ptr(w0, _lib.c_dbl), _lib.ptr(delta_0, _lib.c_dbl), float(alpha_0),
+            float("nan") if beta_0 is None else float(beta_0), int(vb_max_iter), float(epsilon_conv),
+            int(lb_every), *[_lib.ptr(out[k], _lib.c_dbl) for k in ("W", "W_Sigma", "r_nk", "delta", "alpha",
+                                                                    "beta", "pi_k")],
+            _lib.ptr(lb, _lib.c_dbl), cap, C.byref(n_lb), C.byref(n_iter), C.byref(flags)))
+        res = dict(W=out["W"].reshape((M, D, K), order="F"), W_Sigma=out["W_Sigma"].reshape(K, M, D, D),
+                   r_nk=out["r_nk"].reshape((N, K), order="F"), delta=out["delta"], alpha=out["alpha"],
+                   beta=out["beta"], pi_k=out["pi_k"])
+        res.update(lb=lb[:n_lb.value].copy(), n_iter=n_iter.value, flags=flags.value)
+        return res

@@ -116,3 +116,27 @@ def test_device_resident_index_lists_are_validated_on_the_device():
         mb.Engine(bad, tr["basis"])
     with mb.Engine(dev, tr["basis"]) as eng:                   # and the untouched lists pack
         assert eng.layout_info()["pairs"] == int(dev["pair_cell"].shape[0])
+
+
+@pytest.mark.parametrize("G", [2, 3])
+def test_several_shards_behind_one_call_equal_the_single_gpu_fit(G):
+    """melissa_pack_multi + melissa_vb_run_multi (one process, one host thread and stream per shard, partial sums
+    added by the reduce kernel in rank order).  With one GPU in the box all shards land on it -- every line of the
+    multi-GPU path except the NVLink hop is exercised -- otherwise they spread over the first GPUs."""
+    import torch
+    K = 4
+    d, tr = synth.generate(150, 40, K, n_basis=4, seed=12, sites_per_region=60, cov_lo=0.05, cov_hi=0.3)
+    delta_0 = np.full(K, 0.55)
+    with mb.Engine(d, tr["basis"]) as eng:
+        one = eng.run(K, tr["w0"], delta_0, vb_max_iter=30)
+    ndev = torch.cuda.device_count()
+    devices = [g % ndev for g in range(G)]
+    with mb.MultiEngine.pack(d, tr["basis"], G, devices=devices) as me:
+        many = me.run(K, tr["w0"], delta_0, vb_max_iter=30)
+        again = me.run(K, tr["w0"], delta_0, vb_max_iter=30)
+    assert many["n_iter"] == one["n_iter"] and many["flags"] == one["flags"] and len(many["lb"]) == len(one["lb"])
+    np.testing.assert_allclose(many["lb"][1:], one["lb"][1:], rtol=1e-12)          # SURVEY.md 8e: <= 1e-12 drift
+    assert np.array_equal(many["r_nk"].argmax(1), one["r_nk"].argmax(1))
+    np.testing.assert_allclose(many["r_nk"], one["r_nk"], atol=1e-10)
+    np.testing.assert_allclose(many["W"], one["W"], atol=1e-10)
+    assert np.array_equal(again["lb"], many["lb"]) and np.array_equal(again["r_nk"], many["r_nk"])   # reproducible run to run
