@@ -195,6 +195,11 @@ int melissa_vb_run_multi(melissa_multi *mm, int32_t K, const double *w0, const d
                          int32_t *n_iter, int32_t *flags);
 int melissa_multi_free(melissa_multi *mm);
 int32_t melissa_multi_gpus(const melissa_multi *mm);
+/* Device time of the iteration loop of the last melissa_vb_run_multi (CUDA events on every GPU's stream from the
+ * first iteration to the last, set-up and result fetch excluded; the maximum over the GPUs), and the kernels all
+ * shards have launched so far: what bench.py reports for the single-process arm. */
+double melissa_multi_last_loop_ms(const melissa_multi *mm);
+int64_t melissa_multi_launch_count(const melissa_multi *mm);
 
 /* Copy the current state to host buffers (same layouts as melissa_vb_run; NULL skips). */
 int melissa_vb_fetch(melissa_handle *h, double *W, double *W_Sigma, double *r_nk,

@@ -37,6 +37,8 @@ SIGNATURES = {
                                        p_i32, p_i32, p_i32]),
     "melissa_multi_free": (C.c_int, [handle_t]),
     "melissa_multi_gpus": (c_i32, [handle_t]),
+    "melissa_multi_last_loop_ms": (c_dbl, [handle_t]),
+    "melissa_multi_launch_count": (c_i64, [handle_t]),
     "melissa_vb_begin": (C.c_int, [handle_t, c_i32, p_dbl, p_dbl, c_dbl, c_dbl, c_i64, C.c_void_p]),
     "melissa_vb_phase_a": (C.c_int, [handle_t]),
     "melissa_vb_phase_b": (C.c_int, [handle_t, c_i32]),

@@ -1462,7 +1462,6 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
     if (have_host_lists) {
     // ---- validate the pair list on the host (before the first CUDA call when the lists are host memory)
     if (pair_ptr[0] != 0) return fail(MELISSA_ERR_ARG, "pair_ptr[0] must be 0");
-    std::vector<int64_t> reg_cnt((size_t)n_regions + 1, 0);
     {
         // every rule relates pair p to pair p-1 only, so chunks are checked by separate host threads;
         // the failure with the lowest pair index is the one reported
@@ -2274,6 +2273,7 @@ struct melissa_multi {
     std::vector<int64_t> cell_lo;          // first global cell of every shard (G + 1 entries)
     bool own_handles = false;
     int64_t N_total = 0;
+    double last_loop_ms = 0.0;             // iteration loop of the last run: CUDA events per GPU, max over GPUs
 };
 
 int melissa_multi_create(int32_t n_gpus, melissa_handle **handles, melissa_multi **out) {
@@ -2323,6 +2323,12 @@ int melissa_multi_free(melissa_multi *mm) {
 }
 
 int32_t melissa_multi_gpus(const melissa_multi *mm) { return mm ? mm->G : 0; }
+double melissa_multi_last_loop_ms(const melissa_multi *mm) { return mm ? mm->last_loop_ms : 0.0; }
+int64_t melissa_multi_launch_count(const melissa_multi *mm) {
+    int64_t n = 0;
+    if (mm) for (const melissa_handle *h : mm->h) n += h->launches;
+    return n;
+}
 
 int melissa_pack_multi(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const int64_t *pair_ptr,
                        const int32_t *pair_cell, const int32_t *pair_region, const double *x, const uint8_t *y,
@@ -2403,7 +2409,8 @@ int melissa_vb_run_multi(melissa_multi *mm, int32_t K, const double *w0, const d
     struct PerGpu {
         cudaStream_t st = nullptr;
         double *part[2] = {nullptr, nullptr}, *sum = nullptr, *lbsum = nullptr, *orig_red = nullptr, *orig_lb = nullptr;
-        cudaEvent_t ev_part[2] = {nullptr, nullptr}, ev_lb = nullptr;
+        cudaEvent_t ev_part[2] = {nullptr, nullptr}, ev_lb = nullptr, ev_t0 = nullptr, ev_t1 = nullptr;
+        float loop_ms = 0.f;
         int rc = MELISSA_OK;
         std::string err;
     };
@@ -2437,7 +2444,11 @@ int melissa_vb_run_multi(melissa_multi *mm, int32_t K, const double *w0, const d
         if ((rc = dev_alloc(&me.part[1], n_red)) || (rc = dev_alloc(&me.sum, n_red)) || (rc = dev_alloc(&me.lbsum, 2))) { bad(rc); return; }
         for (int q = 0; q < 2; ++q) MG(cudaEventCreateWithFlags(&me.ev_part[q], cudaEventDisableTiming));
         MG(cudaEventCreateWithFlags(&me.ev_lb, cudaEventDisableTiming));
+        MG(cudaEventCreate(&me.ev_t0));
+        MG(cudaEventCreate(&me.ev_t1));
+        MG(cudaStreamSynchronize(me.st));                           // set-up and the first sweep are not part of the loop
         if (!bar.wait()) return;                                    // everybody's buffers and events exist
+        MG(cudaEventRecord(me.ev_t0, me.st));
         for (int i = 2; i <= vb_max_iter; ++i) {                    // :309
             const int par = i & 1;
             h->red = me.part[par];
@@ -2488,7 +2499,9 @@ int melissa_vb_run_multi(melissa_multi *mm, int32_t K, const double *w0, const d
             }
         }
         h->red = me.sum;                                            // what melissa_vb_fetch and a later caller see
+        MG(cudaEventRecord(me.ev_t1, me.st));
         MG(cudaStreamSynchronize(me.st));
+        MG(cudaEventElapsedTime(&me.loop_ms, me.ev_t0, me.ev_t1));
 #undef MG
     };
     std::vector<std::thread> th;
@@ -2523,6 +2536,9 @@ int melissa_vb_run_multi(melissa_multi *mm, int32_t K, const double *w0, const d
         cudaFree(me.part[1]); cudaFree(me.sum); cudaFree(me.lbsum);
         for (int q = 0; q < 2; ++q) if (me.ev_part[q]) cudaEventDestroy(me.ev_part[q]);
         if (me.ev_lb) cudaEventDestroy(me.ev_lb);
+        if (me.ev_t0) cudaEventDestroy(me.ev_t0);
+        if (me.ev_t1) cudaEventDestroy(me.ev_t1);
+        mm->last_loop_ms = g == 0 ? (double)me.loop_ms : std::max(mm->last_loop_ms, (double)me.loop_ms);
         h->stream = nullptr;                                        // the run's stream goes away with the run
         h->begun = false;
         if (me.st) cudaStreamDestroy(me.st);

@@ -267,6 +267,12 @@ class MultiEngine:
         except Exception:
             pass
 
+    def last_loop_ms(self) -> float:
+        return float(self.lib.melissa_multi_last_loop_ms(self.h))
+
+    def launch_count(self) -> int:
+        return int(self.lib.melissa_multi_launch_count(self.h))
+
     def run(self, K, w0, delta_0, alpha_0=0.5, beta_0=None, vb_max_iter=300, epsilon_conv=1e-5, lb_every=10):
         K = int(K)
         w0 = np.asarray(w0, np.float64)
