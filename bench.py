@@ -140,6 +140,121 @@ def host_sample(data_t, n_cells):
                 x=data_t["x"][:c1].cpu().numpy(), y=data_t["y"][:c1].cpu().numpy())
 
 
+def run_single_process(args, wl, config):
+    """`--gpus N` without torchrun: ONE process drives all N GPUs through the C ABI (melissa_multi_create /
+    melissa_vb_run_multi: a host thread and a stream per GPU inside the library, partial sums added over NVLink peer
+    loads).  This is the path an R `.Call` binds; the torchrun arm (one process per GPU, NCCL) stays for the driver."""
+    import numpy as np
+    import torch
+    import melissa_b200 as mb
+    from melissa_b200 import synth
+    G, steps, warmup = args.gpus, args.steps, max(args.warmup, 0)
+    K, D = wl["K"], wl["n_basis"] + 1
+    if torch.cuda.device_count() < G:
+        raise SystemExit("need %d GPUs, found %d" % (G, torch.cuda.device_count()))
+    per = -(-wl["N"] // G)
+    per = -(-per // CHUNK) * CHUNK
+    engines, host_parts, tr = [], [], None
+    P_tot = nnz_tot = 0
+    t_gen = t_pack = 0.0
+    keep_host = not args.no_e2e
+    for g in range(G):
+        lo, hi = min(g * per, wl["N"]), min((g + 1) * per, wl["N"])
+        torch.cuda.set_device(g)
+        t0 = time.time()
+        data_t, tr = synth.generate_device(wl["N"], wl["M"], K, n_basis=wl["n_basis"], seed=wl["seed"], cell_lo=lo,
+                                           cell_hi=hi, N_total=wl["N"], device=g, chunk_cells=CHUNK)
+        torch.cuda.synchronize(g)
+        t_gen += time.time() - t0
+        P_tot += int(data_t["pair_cell"].shape[0])
+        nnz_tot += int(data_t["x"].shape[0])
+        t0 = time.time()
+        engines.append(mb.Engine(data_t, tr["basis"], device=g, allow_empty_regions=True))
+        t_pack += time.time() - t0
+        if keep_host:
+            host_parts.append({k: data_t[k].cpu() for k in ("pair_ptr", "pair_cell", "pair_region", "x", "y")})
+        del data_t
+        torch.cuda.empty_cache()
+    delta_0 = np.full(K, 0.51)
+    me = mb.MultiEngine(engines)
+    if warmup:
+        me.run(K, tr["w0"], delta_0, vb_max_iter=warmup + 1, epsilon_conv=0.0, lb_every=LB_EVERY)
+    sampler = ClockSampler(0)
+    sampler.start()
+    time.sleep(0.15)
+    launches0 = me.launch_count()
+    engines[0].profile(True)
+    out = me.run(K, tr["w0"], delta_0, vb_max_iter=steps + 1, epsilon_conv=0.0, lb_every=LB_EVERY)
+    ms = me.last_loop_ms()
+    launches = me.launch_count() - launches0
+    prof = engines[0].profile_read()
+    engines[0].profile(False)
+    t0 = time.perf_counter()
+    while time.perf_counter() - t0 < 1.0:                      # keep the GPUs busy so the clock sampler sees the loaded state
+        me.run(K, tr["w0"], delta_0, vb_max_iter=steps + 1, epsilon_conv=0.0, lb_every=LB_EVERY)
+    clocks = sampler.finish()
+    info0 = engines[0].layout_info()
+    sweep_ms = prof["sweep"][0] / max(1, prof["sweep"][1])
+    peak, peak_src = measured_peak()
+    alg0 = algorithmic_bytes(info0["cpgs"], info0["pairs"], D)
+    value = P_tot * steps / (ms * 1e-3)
+    line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=G, steps=steps, warmup=warmup, ms_per_step=ms / steps,
+                higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f64", data="synthetic",
+                config=dict(config, sharding="cells over %d GPU(s), one process (melissa_vb_run_multi)" % G))
+    line["roofline"] = dict(bound="hbm", kernel="sweep3_kernel", achieved=alg0 / (sweep_ms * 1e-3) / 1e9, peak=peak, unit="GB/s",
+                            frac=alg0 / (sweep_ms * 1e-3) / 1e9 / peak, traffic=None, peak_source=peak_src,
+                            algorithmic_bytes_per_launch=alg0, kernel_ms=sweep_ms, note="GPU 0's shard")
+    line["kernels_ms_per_step"] = {k: v[0] / steps for k, v in prof.items()}
+    line["gpu_launches"] = launches
+    line["clocks"] = clocks
+    line["pairs"], line["cpgs"] = P_tot, nnz_tot
+    line["setup_s"] = dict(generate=round(t_gen, 2), pack=round(t_pack, 2))
+    line["check"] = dict(ari_vs_truth=mb.cluster_ari(tr["C_true"], out["r_nk"]), last_lb=float(out["lb"][-1]))
+    t0 = time.perf_counter()
+    conv = me.run(K, tr["w0"], delta_0, vb_max_iter=300, epsilon_conv=1e-5, lb_every=LB_EVERY)
+    line["time_to_converge"] = dict(seconds=time.perf_counter() - t0, iterations=int(conv["n_iter"]) - 1, flags=int(conv["flags"]),
+                                    lb=float(conv["lb"][-1]), rule="abs(LB - LB_prev) < 1e-5 every 10th iteration, vb_max_iter = 300")
+    me.close()
+    for e in engines:
+        e.close()
+    torch.cuda.empty_cache()
+    e2e = None
+    if keep_host:
+        try:
+            # the whole job as ONE set of pinned host arrays, the way a caller of melissa_pack_multi holds it
+            tot = {k: sum(int(h[k].shape[0]) for h in host_parts) for k in ("pair_cell", "x")}
+            hp = torch.empty(tot["pair_cell"] + 1, dtype=torch.int64, pin_memory=True)
+            hc = torch.empty(tot["pair_cell"], dtype=torch.int32, pin_memory=True)
+            hr = torch.empty(tot["pair_cell"], dtype=torch.int32, pin_memory=True)
+            hx = torch.empty(tot["x"], dtype=torch.float64, pin_memory=True)
+            hy = torch.empty(tot["x"], dtype=torch.uint8, pin_memory=True)
+            p0 = i0 = c0 = 0
+            hp[0] = 0
+            for g, h in enumerate(host_parts):
+                n_p, n_i = int(h["pair_cell"].shape[0]), int(h["x"].shape[0])
+                hp[p0 + 1:p0 + n_p + 1] = h["pair_ptr"][1:] + i0
+                hc[p0:p0 + n_p] = h["pair_cell"] + c0
+                hr[p0:p0 + n_p] = h["pair_region"]
+                hx[i0:i0 + n_i] = h["x"]
+                hy[i0:i0 + n_i] = h["y"]
+                p0, i0, c0 = p0 + n_p, i0 + n_i, c0 + int(h["pair_cell"][-1]) + 1
+            host_parts.clear()
+            hd = mb.MelissaData(N=wl["N"], M=wl["M"], pair_ptr=hp.numpy(), pair_cell=hc.numpy(), pair_region=hr.numpy(),
+                                x=hx.numpy(), y=hy.numpy())
+            t0 = time.perf_counter()
+            with mb.MultiEngine.pack(hd, tr["basis"], G) as me2:
+                o2 = me2.run(K, tr["w0"], delta_0, vb_max_iter=steps + 1, epsilon_conv=0.0, lb_every=LB_EVERY)
+            dt = time.perf_counter() - t0
+            h2d = hp.numel() * 8 + hc.numel() * 4 + hr.numel() * 4 + hx.numel() * 8 + hy.numel() + tr["w0"].nbytes
+            d2h = sum(np.asarray(o2[k]).nbytes for k in ("W", "W_Sigma", "r_nk", "delta", "beta", "pi_k"))
+            e2e = dict(value=P_tot * steps / dt, unit=UNIT, h2d_bytes_per_step=h2d / steps, d2h_bytes_per_step=d2h / steps, seconds=dt,
+                       what="melissa_pack_multi + melissa_vb_run_multi(%d iterations) + result fetch, pinned host buffers, one process" % steps)
+        except Exception as exc:  # reported, never hidden
+            e2e = dict(value=None, unit=UNIT, error=repr(exc))
+    line["e2e"] = e2e
+    print(json.dumps(line))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -162,6 +277,8 @@ def main():
                   l2="inputs larger than L2 (no flush needed)")
 
     import numpy as np
+    if args.impl == "ours" and args.gpus > 1 and world == 1:
+        return run_single_process(args, wl, config)
     if args.impl == "reference":
         # The reference is interpreted R (no R on this box): its algorithm as restated in oracle/ (plain C,
         # every host thread), on a bounded sample of the same workload.  Rank 0 only.
