@@ -154,7 +154,7 @@ def run_single_process(args, wl, config):
         raise SystemExit("need %d GPUs, found %d" % (G, torch.cuda.device_count()))
     per = -(-wl["N"] // G)
     per = -(-per // CHUNK) * CHUNK
-    engines, host_parts, tr = [], [], None
+    engines, host_parts, tr, c_true = [], [], None, []
     P_tot = nnz_tot = 0
     t_gen = t_pack = 0.0
     keep_host = not args.no_e2e
@@ -166,6 +166,7 @@ def run_single_process(args, wl, config):
                                            cell_hi=hi, N_total=wl["N"], device=g, chunk_cells=CHUNK)
         torch.cuda.synchronize(g)
         t_gen += time.time() - t0
+        c_true.append(np.asarray(tr["C_true"]))
         P_tot += int(data_t["pair_cell"].shape[0])
         nnz_tot += int(data_t["x"].shape[0])
         t0 = time.time()
@@ -209,7 +210,7 @@ def run_single_process(args, wl, config):
     line["clocks"] = clocks
     line["pairs"], line["cpgs"] = P_tot, nnz_tot
     line["setup_s"] = dict(generate=round(t_gen, 2), pack=round(t_pack, 2))
-    line["check"] = dict(ari_vs_truth=mb.cluster_ari(tr["C_true"], out["r_nk"]), last_lb=float(out["lb"][-1]))
+    line["check"] = dict(ari_vs_truth=mb.cluster_ari(np.concatenate(c_true), out["r_nk"]), last_lb=float(out["lb"][-1]))
     t0 = time.perf_counter()
     conv = me.run(K, tr["w0"], delta_0, vb_max_iter=300, epsilon_conv=1e-5, lb_every=LB_EVERY)
     line["time_to_converge"] = dict(seconds=time.perf_counter() - t0, iterations=int(conv["n_iter"]) - 1, flags=int(conv["flags"]),
