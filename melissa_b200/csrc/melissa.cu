@@ -1113,8 +1113,8 @@ int finish_sliced(melissa_handle *h, Sliced *sl, int64_t *d_src, cudaStream_t st
     cudaMemsetAsync(sl->x_sell + sl->x_len, 0, (size_t)2 * SWEEP3_NST * SWEEP3_XU * 32 * sizeof(double), st);
     CU(cudaStreamWaitEvent(st, xy_arrived, 0));                 // the flat x / y must be on the device from here on
     const int grid = (int)((S * 32 + 255) / 256);
-    sell_fill_kernel<<<grid, 256, 0, st>>>(h->x, h->y, d_src, sl->lane_meta, sl->slice_xbase, sl->slice_ybase, sl->slice_len,
-                                    sl->x_sell, sl->ybits, S);
+    sell_fill_kernel<<<(int)std::min<int64_t>((S + 3) / 4, (int64_t)h->sm_count * 32), 128, 0, st>>>(
+        h->x, h->y, d_src, sl->lane_meta, sl->slice_xbase, sl->slice_ybase, sl->slice_len, sl->x_sell, sl->ybits, S);
     {
         auto run = [&]() -> int {
             DISPATCH_D(h->D, hh_sliced_kernel<DD><<<grid, 256, 0, st>>>(sl->x_sell, sl->slice_xbase, sl->lane_meta, sl->stats,

@@ -147,29 +147,42 @@ __device__ __forceinline__ double trunc_mean3(double t, const double *__restrict
     return t + y;
 }
 
-// Re-lay x / y into slices.  One thread per (slice, lane).
-__global__ void sell_fill_kernel(const double *__restrict__ x, const uint8_t *__restrict__ y,
-                                 const int64_t *__restrict__ lane_src, const int32_t *__restrict__ lane_meta,
-                                 const int64_t *__restrict__ slice_xbase, const int64_t *__restrict__ slice_ybase,
-                                 const int32_t *__restrict__ slice_len, double *__restrict__ x_sell,
-                                 uint32_t *__restrict__ ybits, int64_t S) {
-    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= S * 32) return;
-    const int64_t s = t >> 5;
-    const int lane = (int)(t & 31);
-    const int L = slice_len[s], len = lane_meta[t] & 0xffff;
-    const int64_t src = lane_src[t], xb = slice_xbase[s], yb = slice_ybase[s];
-    uint32_t word = 0;
-    for (int i = 0; i < L; ++i) {
-        double xv = 0.0;
-        if (i < len) {
-            xv = x[src + i];
-            word |= (uint32_t)(y[src + i] != 0) << (i & 31);
-        }
-        x_sell[xb + (int64_t)i * 32 + lane] = xv;
-        if ((i & 31) == 31 || i == L - 1) {
-            ybits[yb + (int64_t)(i >> 5) * 32 + lane] = word;
-            word = 0;
+// Re-lay x / y into slices.  One WARP per slice, 32 rows at a time through a shared-memory tile: the
+// flat arrays are read in runs (the CpGs of one pair are contiguous), the slice is written row by row
+// (256 contiguous bytes), so both sides of the transposition are coalesced.
+__global__ void __launch_bounds__(128)
+sell_fill_kernel(const double *__restrict__ x, const uint8_t *__restrict__ y, const int64_t *__restrict__ lane_src,
+                 const int32_t *__restrict__ lane_meta, const int64_t *__restrict__ slice_xbase,
+                 const int64_t *__restrict__ slice_ybase, const int32_t *__restrict__ slice_len,
+                 double *__restrict__ x_sell, uint32_t *__restrict__ ybits, int64_t S) {
+    __shared__ double tile[4][32][33];                     // [warp][pair][row], padded against bank conflicts
+    __shared__ uint32_t ytile[4][32];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int64_t s = (int64_t)blockIdx.x * 4 + warp; s < S; s += (int64_t)gridDim.x * 4) {
+        const int L = slice_len[s];
+        const int my_len = lane_meta[s * 32 + lane] & 0xffff;
+        const int64_t my_src = lane_src[s * 32 + lane], xb = slice_xbase[s], yb = slice_ybase[s];
+        for (int i0 = 0; i0 < L; i0 += 32) {
+            // rows i0 .. i0 + 31 of every pair of the slice: lane = row while reading, lane = pair while writing
+            for (int l = 0; l < 32; ++l) {
+                const int len = __shfl_sync(0xffffffffu, my_len, l);
+                const int64_t src = __shfl_sync(0xffffffffu, my_src, l);
+                const int i = i0 + lane;
+                double xv = 0.0;
+                uint32_t bit = 0;
+                if (i < len) {
+                    xv = x[src + i];
+                    bit = y[src + i] != 0;
+                }
+                tile[warp][l][lane] = xv;
+                const uint32_t word = __ballot_sync(0xffffffffu, bit);
+                if (lane == 0) ytile[warp][l] = word;
+            }
+            __syncwarp();
+            const int rows = min(32, L - i0);
+            for (int r = 0; r < rows; ++r) x_sell[xb + (int64_t)(i0 + r) * 32 + lane] = tile[warp][lane][r];
+            ybits[yb + (int64_t)(i0 >> 5) * 32 + lane] = ytile[warp][lane];
+            __syncwarp();
         }
     }
 }
