@@ -27,6 +27,8 @@ WORKLOADS = {
                N=20000, M=5000, K=10, n_basis=4, seed=2),
     "c3": dict(name="synthetic 5,000 cells x 1,000 regions, K=4, RBF M=4, ~25 CpGs/pair (BASELINE configs[2])",
                N=5000, M=1000, K=4, n_basis=4, seed=1),
+    "c5": dict(name="synthetic 100,000 cells x 10,000 regions, K=20, RBF M=4, ~25 CpGs/pair (BASELINE configs[4]; needs 8 GPUs)",
+               N=100000, M=10000, K=20, n_basis=4, seed=3),
     "tiny": dict(name="synthetic 500 cells x 200 regions, K=3 (development only)", N=500, M=200, K=3, n_basis=4, seed=3),
 }
 METRIC = "VB cell-region updates/s"

@@ -673,9 +673,10 @@ __global__ void lanes_to_pairs_kernel(const double *__restrict__ src, const int3
 struct StageTimer {       // MELISSA_PACK_TIMING=1 prints where melissa_pack spends its time
     bool on = std::getenv("MELISSA_PACK_TIMING") != nullptr;
     std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    bool sync = on && std::strcmp(std::getenv("MELISSA_PACK_TIMING"), "2") != 0;     // "2": host clock only, no device sync
     void lap(const char *what) {
         if (!on) return;
-        cudaDeviceSynchronize();
+        if (sync) cudaDeviceSynchronize();
         const auto t1 = std::chrono::steady_clock::now();
         std::fprintf(stderr, "[melissa_pack] %-28s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
         t0 = t1;
