@@ -187,7 +187,10 @@ def run_single_process(args, wl, config):
     time.sleep(0.15)
     launches0 = me.launch_count()
     engines[0].profile(True)
-    out = me.run(K, tr["w0"], delta_0, vb_max_iter=steps + 1, epsilon_conv=0.0, lb_every=LB_EVERY)
+    # one bound in `steps` iterations, like the stepping arm (the run always takes a bound at vb_max_iter, so a second
+    # one at a multiple of 10 is switched off when the run is that short)
+    lb_every_run = LB_EVERY if steps > LB_EVERY else steps + 1
+    out = me.run(K, tr["w0"], delta_0, vb_max_iter=steps + 1, epsilon_conv=0.0, lb_every=lb_every_run)
     ms = me.last_loop_ms()
     launches = me.launch_count() - launches0
     prof = engines[0].profile_read()

@@ -997,29 +997,23 @@ int build_slice_index_host(melissa_handle *h, Sliced *sl, const int64_t *pair_pt
             for (size_t q = 0; q < reg.size(); ++q) reg_slice[(size_t)cur[reg[q]]++] = (int32_t)(soff[(size_t)t] + (int64_t)q);
         }
     }
-    // ---- chunks of the sweep: runs of consecutive slices that stay inside one cell block
-    std::vector<int32_t> chunk_ptr;
+    // ---- chunks of the sweep (make_chunks, pack_gpu.cuh)
+    std::vector<int64_t> blk_first((size_t)sl->NB + 1, S);
     {
-        // (a chunk adds to a shared accumulator at most once per slice; LIMB_MAX_ADDS is what its limbs can absorb)
-        const int64_t target = std::min<int64_t>(LIMB_MAX_ADDS, g_opt_sweep_chunk > 0
-                                   ? g_opt_sweep_chunk
-                                   : std::max<int64_t>(384, std::min<int64_t>(2048, S / ((int64_t)h->sm_count * 16))));
         int64_t s0 = 0;
+        int last = -1;
         for (int t = 0; t < nthr; ++t) {
             const auto &cbv = parts[(size_t)t].slice_cb;
-            size_t q = 0;
-            while (q < cbv.size()) {
-                size_t e = q;
-                while (e < cbv.size() && cbv[e] == cbv[q]) ++e;          // [q, e): the slices of one cell block
-                const int64_t n = (int64_t)(e - q), pieces = std::max<int64_t>(1, (n + target - 1) / target);
-                for (int64_t c = 0; c < pieces; ++c) chunk_ptr.push_back((int32_t)(s0 + (int64_t)q + n * c / pieces));
-                q = e;
-            }
+            for (size_t q = 0; q < cbv.size(); ++q)
+                if (cbv[q] != last) {
+                    for (int c = last + 1; c <= cbv[q]; ++c) blk_first[(size_t)c] = s0 + (int64_t)q;
+                    last = cbv[q];
+                }
             s0 += (int64_t)cbv.size();
         }
-        chunk_ptr.push_back((int32_t)S);
-        sl->NC = (int)chunk_ptr.size() - 1;
     }
+    const std::vector<int32_t> chunk_ptr = make_chunks(blk_first, S, h->sm_count, g_opt_sweep_chunk);
+    sl->NC = (int)chunk_ptr.size() - 1;
     tm.lap("region index");
     // ---- upload, piece by piece
     int rc;

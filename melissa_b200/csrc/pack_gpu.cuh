@@ -138,6 +138,34 @@ struct MaxOp {
     __device__ __forceinline__ int32_t operator()(int32_t a, int32_t b) const { return a > b ? a : b; }
 };
 
+// Chunks of the sweep: runs of consecutive slices that stay inside one cell block (blk_first[cb] = first slice of
+// block cb, blk_first[NB] = S).  A CTA claims chunks in list order, so the list starts with large chunks (few
+// barriers and flushes) and ends with small ones (the CTAs finish together): full size for the first half of the
+// slices, a half up to 80 %, a quarter after that.
+std::vector<int32_t> make_chunks(const std::vector<int64_t> &blk_first, int64_t S, int sm_count, int chunk_opt) {
+    // (a chunk adds to a shared accumulator at most once per slice; LIMB_MAX_ADDS is what its limbs can absorb)
+    const int64_t base = std::min<int64_t>(LIMB_MAX_ADDS, chunk_opt > 0 ? chunk_opt
+                                               : std::max<int64_t>(256, std::min<int64_t>(2048, S / ((int64_t)sm_count * 8))));
+    std::vector<int32_t> chunk_ptr;
+    const size_t NB = blk_first.size() - 1;
+    for (size_t cb = 0; cb < NB; ++cb) {
+        int64_t q = blk_first[cb];
+        const int64_t e = blk_first[cb + 1];
+        while (q < e) {
+            int64_t target = base;
+            if (chunk_opt <= 0) {
+                if (q * 10 >= S * 8) target = std::max<int64_t>(48, base / 4);
+                else if (q * 2 >= S) target = std::max<int64_t>(96, base / 2);
+            }
+            const int64_t left = e - q, pieces = (left + target - 1) / target;
+            chunk_ptr.push_back((int32_t)q);
+            q += (left + pieces - 1) / pieces;
+        }
+    }
+    chunk_ptr.push_back((int32_t)S);
+    return chunk_ptr;
+}
+
 // Everything index-related of the sliced layout, from DEVICE index lists, on `st`.  x / y are not touched here.
 // On return sl holds S, the slice / lane arrays, xbase / ybase, x_len / y_len, blk_cells, reg_slice(_ptr),
 // chunk_ptr and d_src_out (the CpG offset of every lane in the flat x / y, for the fill kernel; caller frees).
@@ -259,22 +287,9 @@ int build_slice_index_device(melissa_handle *h, Sliced *sl, const int64_t *d_ptr
     (void)blk_first;
     sl->x_len = tot[0];
     sl->y_len = tot[1];
-    // ---- chunks of the sweep: runs of consecutive slices that stay inside one cell block
-    std::vector<int32_t> chunk_ptr;
-    {
-        // (a chunk adds to a shared accumulator at most once per slice; LIMB_MAX_ADDS is what its limbs can absorb)
-        const int64_t target = std::min<int64_t>(LIMB_MAX_ADDS, sweep_chunk_opt > 0
-                                   ? sweep_chunk_opt
-                                   : std::max<int64_t>(384, std::min<int64_t>(2048, S / ((int64_t)h->sm_count * 16))));
-        for (int cb = 0; cb < NB; ++cb) {
-            const int64_t q = blk64[(size_t)cb], n = blk64[(size_t)cb + 1] - q;
-            if (n <= 0) continue;
-            const int64_t pieces = std::max<int64_t>(1, (n + target - 1) / target);
-            for (int64_t c = 0; c < pieces; ++c) chunk_ptr.push_back((int32_t)(q + n * c / pieces));
-        }
-        chunk_ptr.push_back((int32_t)S);
-        sl->NC = (int)chunk_ptr.size() - 1;
-    }
+    // ---- chunks of the sweep
+    const std::vector<int32_t> chunk_ptr = make_chunks(blk64, S, h->sm_count, sweep_chunk_opt);
+    sl->NC = (int)chunk_ptr.size() - 1;
     if ((rc = dev_alloc(&sl->chunk_ptr, (int64_t)chunk_ptr.size()))) return done(rc);
     CU(cudaMemcpyAsync(sl->chunk_ptr, chunk_ptr.data(), chunk_ptr.size() * 4, cudaMemcpyHostToDevice, st));
     CU(cudaStreamSynchronize(st));
