@@ -654,6 +654,7 @@ __global__ void impute_kernel(const int64_t *__restrict__ pair_ptr, const int32_
 
 #include "sliced.cuh"
 #include "sweep3.cuh"
+#include "contract_tma.cuh"
 
 // Per-lane values back into the caller's pair order: out[pair][d] = src[slice * 32 + lane][d], or, with
 // from_stats, the g = H^T E[z] part of the lane's record in the tile-ordered stats array.
@@ -1327,12 +1328,26 @@ int launch_sweep3(melissa_handle *h, bool with_lb) {
 }
 
 int g_opt_contract_mma = 1;
+int g_opt_contract_tma = 1;
 
 template <int MT, int NT>
 int launch_contract_mma_t(melissa_handle *h, int block) {
     Sliced *sl = h->sl;
     const size_t smem = (size_t)(block / 32) * MT * NT * 64 * sizeof(double);
     auto kfn = contract_mma_kernel<MT, NT>;
+    if (smem > 48 * 1024) CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kfn<<<h->M, block, smem, h->stream>>>(sl->reg_slice_ptr, sl->reg_slice, sl->lane_cell, sl->stats, h->r, h->red,
+                                         h->K, h->R);
+    return MELISSA_OK;
+}
+
+template <int MT, int NT>
+int launch_contract_tma_t(melissa_handle *h, int block) {
+    Sliced *sl = h->sl;
+    const int nw = block / 32;
+    const size_t ring = (size_t)nw * CTMA_NST * ((size_t)h->R * 256 + 128) + (size_t)nw * CTMA_NST * 8;
+    const size_t smem = std::max(ring, (size_t)nw * MT * NT * 64 * sizeof(double));
+    auto kfn = contract_tma_kernel<MT, NT>;
     if (smem > 48 * 1024) CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kfn<<<h->M, block, smem, h->stream>>>(sl->reg_slice_ptr, sl->reg_slice, sl->lane_cell, sl->stats, h->r, h->red,
                                          h->K, h->R);
@@ -1351,7 +1366,9 @@ int launch_contract_v2(melissa_handle *h) {
         while (nw > 1 && avg_slices / nw < 4) nw >>= 1;
         const int block = 32 * nw;
         int rc = MELISSA_OK;
-#define CMMA(MT_, NT_) if (MT == MT_ && NT == NT_) { rc = launch_contract_mma_t<MT_, NT_>(h, block); done = true; }
+        // operand staged by the bulk-copy engine (contract_tma.cuh) unless switched off ("contract_tma" option)
+#define CMMA(MT_, NT_) if (MT == MT_ && NT == NT_) { rc = g_opt_contract_tma ? launch_contract_tma_t<MT_, NT_>(h, block) \
+                                                                             : launch_contract_mma_t<MT_, NT_>(h, block); done = true; }
         CMMA(1, 1) CMMA(1, 2) CMMA(1, 3) CMMA(1, 4) CMMA(1, 5) CMMA(1, 6)
         CMMA(2, 1) CMMA(2, 2) CMMA(2, 3) CMMA(2, 4) CMMA(2, 5) CMMA(2, 6)
         CMMA(3, 3) CMMA(3, 6) CMMA(4, 3) CMMA(4, 6)
@@ -1765,6 +1782,10 @@ int melissa_set_option(const char *key, int64_t value) {
     }
     if (!std::strcmp(key, "contract_mma")) {
         g_opt_contract_mma = value != 0;
+        return MELISSA_OK;
+    }
+    if (!std::strcmp(key, "contract_tma")) {
+        g_opt_contract_tma = value != 0;
         return MELISSA_OK;
     }
     if (!std::strcmp(key, "sliced")) {

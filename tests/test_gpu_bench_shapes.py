@@ -140,3 +140,22 @@ def test_several_shards_behind_one_call_equal_the_single_gpu_fit(G):
     np.testing.assert_allclose(many["r_nk"], one["r_nk"], atol=1e-10)
     np.testing.assert_allclose(many["W"], one["W"], atol=1e-10)
     assert np.array_equal(again["lb"], many["lb"]) and np.array_equal(again["r_nk"], many["r_nk"])   # reproducible run to run
+
+
+def test_tma_staged_contraction_equals_the_plain_load_one():
+    """contract_tma_kernel (cp.async.bulk + mbarrier staging) walks the slices in the same order as
+    contract_mma_kernel and feeds the same tiles to the same DMMA sequence: the fits must agree to the last bit."""
+    K = 10
+    d, tr = synth.generate(400, 50, K, n_basis=4, seed=13, sites_per_region=60, cov_lo=0.05, cov_hi=0.3)
+    delta_0 = np.full(K, 0.55)
+    out = {}
+    for tma in (1, 0):
+        mb.set_option("contract_tma", tma)
+        try:
+            with mb.Engine(d, tr["basis"]) as eng:
+                out[tma] = eng.run(K, tr["w0"], delta_0, vb_max_iter=20)
+        finally:
+            mb.set_option("contract_tma", 1)
+    assert np.array_equal(out[0]["lb"], out[1]["lb"])
+    assert np.array_equal(out[0]["W"], out[1]["W"])
+    assert np.array_equal(out[0]["r_nk"], out[1]["r_nk"])
