@@ -65,7 +65,7 @@ int fail(int code, const char *fmt, ...) {
                         cudaGetErrorString(e_));                                          \
     } while (0)
 
-constexpr int MAX_D = 8;        // basis$M <= 7 (the reference's experiments use M = 3, 4, 7)
+constexpr int MAX_D = 16;       // basis$M <= 15 (the reference's scripts go up to M = 11) (the reference's experiments use M = 3, 4, 7)
 constexpr int MAX_MUS = 15;
 
 struct BasisDev {
@@ -133,6 +133,7 @@ struct melissa_handle {
     Sliced *sl = nullptr;                  // v2 layout (sliced.cuh); null = v1 path
     int sweep_cfg[2] = {0, 0};             // sweep variants whose function attributes have been set
     int sweep_warps = 0;                   // warps per CTA of the sweep for this fit's K (0 = does not fit)
+    bool sweep_direct = false;             // the sweep's E-step sums go straight to global memory (very large K)
 };
 
 namespace {
@@ -726,6 +727,14 @@ int grid_for(int64_t work, int block, int sm_count, int per_sm) {
         case 6: { constexpr int DD = 6; __VA_ARGS__; } break;                     \
         case 7: { constexpr int DD = 7; __VA_ARGS__; } break;                     \
         case 8: { constexpr int DD = 8; __VA_ARGS__; } break;                     \
+        case 9: { constexpr int DD = 9; __VA_ARGS__; } break;                     \
+        case 10: { constexpr int DD = 10; __VA_ARGS__; } break;                   \
+        case 11: { constexpr int DD = 11; __VA_ARGS__; } break;                   \
+        case 12: { constexpr int DD = 12; __VA_ARGS__; } break;                   \
+        case 13: { constexpr int DD = 13; __VA_ARGS__; } break;                   \
+        case 14: { constexpr int DD = 14; __VA_ARGS__; } break;                   \
+        case 15: { constexpr int DD = 15; __VA_ARGS__; } break;                   \
+        case 16: { constexpr int DD = 16; __VA_ARGS__; } break;                   \
         default: return fail(MELISSA_ERR_ARG, "unsupported D = %d", D_);          \
     }
 
@@ -767,6 +776,12 @@ int launch_contract(melissa_handle *h) {
     } else if (J == 2) {
         if (h->K <= 4) CONTRACT(2, 4);
         else CONTRACT(2, 8);
+    } else if (J == 3) {
+        CONTRACT(3, 4);
+    } else if (J == 4) {
+        CONTRACT(4, 4);
+    } else if (J == 5) {
+        CONTRACT(5, 4);
     } else {
         return fail(MELISSA_ERR_ARG, "record length %d not supported", h->R);
     }
@@ -1131,20 +1146,26 @@ int finish_sliced(melissa_handle *h, Sliced *sl, int64_t *d_src, cudaStream_t st
 
 // Shared memory of one sweep CTA with nw warps: the two tables, the block's fixed-point sums,
 // one U[m] staging area per warp, lb sums and control words.
-size_t sweep3_smem(const melissa_handle *h, int nw) {
+size_t sweep3_smem(const melissa_handle *h, int nw, bool direct = false) {
     const Sliced *sl = h->sl;
     const size_t UR = ((size_t)h->K * h->R + 1) & ~(size_t)1;
     return (size_t)sl->rt.n_entries * sizeof(double2) + ((size_t)MILLS_N + 1) * sizeof(double) +
-           4 * (size_t)sl->Tn * h->K * sizeof(unsigned int) + (size_t)nw * UR * sizeof(double) +
+           (direct ? 0 : 4 * (size_t)sl->Tn * h->K * sizeof(unsigned int)) + (size_t)nw * UR * sizeof(double) +
            (size_t)nw * SWEEP3_NST * SWEEP3_XU * 32 * sizeof(double) + 4 * 8 + 16;
 }
 
 // Most warps (of SWEEP3_THREADS / 32) whose staging areas still fit next to the rest; 0 = not even four.
-int sweep3_warps(const melissa_handle *h) {
-    int nw = SWEEP3_THREADS / 32;
-    if (g_opt_sweep_warps > 0) nw = std::min(nw, g_opt_sweep_warps);
-    for (; nw >= 4; nw -= 2)
+// When the block sums (Tn x K x 16 bytes) leave no room for at least eight warps the sweep runs without them
+// ("direct": its E-step terms go to global memory with 64-bit atomics -- slower, but any K fits).
+int sweep3_warps(const melissa_handle *h, bool *direct) {
+    int nw0 = SWEEP3_THREADS / 32;
+    if (g_opt_sweep_warps > 0) nw0 = std::min(nw0, g_opt_sweep_warps);
+    *direct = false;
+    for (int nw = nw0; nw >= std::min(8, nw0); nw -= 2)
         if (sweep3_smem(h, nw) <= 227u * 1024) return nw;
+    *direct = true;
+    for (int nw = nw0; nw >= 2; nw -= 2)
+        if (sweep3_smem(h, nw, true) <= 227u * 1024) return nw;
     return 0;
 }
 
@@ -1296,8 +1317,9 @@ int launch_sweep3(melissa_handle *h, bool with_lb) {
     if (nw == 0)
         return fail(MELISSA_ERR_ARG, "K = %d with cell blocks of %d does not fit the sweep's shared memory; "
                     "pack with a smaller \"cell_block\" option", h->K, sl->Tn);
-    const size_t smem = sweep3_smem(h, nw);
+    const size_t smem = sweep3_smem(h, nw, h->sweep_direct);
     Sweep3Args a;
+    a.direct = h->sweep_direct ? 1 : 0;
     a.x_sell = sl->x_sell; a.ybits = sl->ybits; a.slice_xbase = sl->slice_xbase; a.slice_ybase = sl->slice_ybase;
     a.slice_len = sl->slice_len; a.slice_region = sl->slice_region; a.slice_cb = sl->slice_cb;
     a.lane_cell = sl->lane_cell; a.lane_meta = sl->lane_meta; a.blk_cells = sl->blk_cells;
@@ -1369,9 +1391,11 @@ int launch_contract_v2(melissa_handle *h) {
         // operand staged by the bulk-copy engine (contract_tma.cuh) unless switched off ("contract_tma" option)
 #define CMMA(MT_, NT_) if (MT == MT_ && NT == NT_) { rc = g_opt_contract_tma ? launch_contract_tma_t<MT_, NT_>(h, block) \
                                                                              : launch_contract_mma_t<MT_, NT_>(h, block); done = true; }
+        // every K <= 32 (MT <= 4) with every D <= 8 (R <= 44, NT <= 6); beyond that the CUDA-core kernel below
         CMMA(1, 1) CMMA(1, 2) CMMA(1, 3) CMMA(1, 4) CMMA(1, 5) CMMA(1, 6)
         CMMA(2, 1) CMMA(2, 2) CMMA(2, 3) CMMA(2, 4) CMMA(2, 5) CMMA(2, 6)
-        CMMA(3, 3) CMMA(3, 6) CMMA(4, 3) CMMA(4, 6)
+        CMMA(3, 1) CMMA(3, 2) CMMA(3, 3) CMMA(3, 4) CMMA(3, 5) CMMA(3, 6)
+        CMMA(4, 1) CMMA(4, 2) CMMA(4, 3) CMMA(4, 4) CMMA(4, 5) CMMA(4, 6)
 #undef CMMA
         if (rc) return rc;
     }
@@ -1840,7 +1864,7 @@ int melissa_free(melissa_handle *h) {
 int melissa_vb_begin(melissa_handle *h, int32_t K, const double *w0, const double *delta_0,
                      double alpha_0, double beta_0, int64_t n_cells_total, void *stream) {
     if (!h) return fail(MELISSA_ERR_ARG, "handle is NULL");
-    if (K <= 0 || K > 64) return fail(MELISSA_ERR_ARG, "K must be in 1..64");
+    if (K <= 0 || K > 256) return fail(MELISSA_ERR_ARG, "K must be in 1..256");
     if (!w0 || !delta_0) return fail(MELISSA_ERR_ARG, "w0 / delta_0 is NULL");
     if (n_cells_total < h->N) return fail(MELISSA_ERR_ARG, "n_cells_total < cells in this shard");
     for (int k = 0; k < K; ++k)
@@ -1900,7 +1924,7 @@ int melissa_vb_begin(melissa_handle *h, int32_t K, const double *w0, const doubl
     h->begun = true;
     // mu from rowMeans(w), E[z], E-step terms for i = 2  (R/melissa_vb.R:283-302)
     if (h->sl) {
-        h->sweep_warps = sweep3_warps(h);
+        h->sweep_warps = sweep3_warps(h, &h->sweep_direct);
         // rowMeans over clusters = responsibilities 1/K for every cell in this first sweep
         fill_kernel<<<grid_for((int64_t)h->N * K, 256, h->sm_count, 8), 256, 0, st>>>(h->r, (int64_t)h->N * K, 1.0 / (double)K);
         h->launches++;

@@ -34,6 +34,7 @@ struct Sweep3Args {
     RbfTab rt;
     BasisDev basis;
     int K, Tn, NC, G;
+    int direct;                               // 1: no shared block sums (K too large for them): E-step terms go straight to log_rho_fx
     unsigned int *chunk_counter;
 };
 
@@ -69,13 +70,14 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
     double2 *s_rbf = reinterpret_cast<double2 *>(smem_raw);
     double *s_mills = reinterpret_cast<double *>(s_rbf + a.rt.n_entries);
     unsigned int *s_acc = reinterpret_cast<unsigned int *>(s_mills + MILLS_N + 1);      // [4 limbs][K][Tn]
-    double *s_u = reinterpret_cast<double *>(s_acc + 4 * (size_t)Tn * K);
+    double *s_u = reinterpret_cast<double *>(s_acc + (a.direct ? 0 : 4 * (size_t)Tn * K));
     double *s_x = s_u + (size_t)nw * UR;                                                         // per-warp ring of x groups
     unsigned long long *s_lb = reinterpret_cast<unsigned long long *>(s_x + (size_t)nw * NST * XU * 32);   // [2] + wrong-side count
     int *s_ctl = reinterpret_cast<int *>(s_lb + 4);                                             // cursor, next chunk
     for (int i = threadIdx.x; i < a.rt.n_entries; i += blockDim.x) s_rbf[i] = a.rbf_tab[i];
     for (int i = threadIdx.x; i < MILLS_N; i += blockDim.x) s_mills[i] = a.mills_tab[i];
-    for (int i = threadIdx.x; i < 4 * Tn * K; i += blockDim.x) s_acc[i] = 0u;
+    if (!a.direct)
+        for (int i = threadIdx.x; i < 4 * Tn * K; i += blockDim.x) s_acc[i] = 0u;
     if (threadIdx.x < 4) s_lb[threadIdx.x] = 0ull;
     if (threadIdx.x == 0) s_ctl[1] = (int)atomicAdd(a.chunk_counter, 1u);
     __syncthreads();
@@ -340,8 +342,14 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
                         const bool two = k + 1 < K;
                         const double v1 = two ? term(k + 1, trc1) : 0.0;
                         over |= !(fabs(v0) < LIMB_LIMIT) || !(fabs(v1) < LIMB_LIMIT);
-                        limb_add_shared(acc + k * Tn, K * Tn, v0);
-                        if (two) limb_add_shared(acc + (k + 1) * Tn, K * Tn, v1);
+                        if (!a.direct) {
+                            limb_add_shared(acc + k * Tn, K * Tn, v0);
+                            if (two) limb_add_shared(acc + (k + 1) * Tn, K * Tn, v1);
+                        } else {
+                            unsigned long long *gacc = a.log_rho_fx + 2 * ((int64_t)cell * K + k);
+                            fx_add(gacc, fx_from_double(v0));
+                            if (two) fx_add(gacc + 2, fx_from_double(v1));
+                        }
                         if (WITH_LB) {
                             lb_s = fma(rp[k], trc0, lb_s);
                             if (two) lb_s = fma(rp[k + 1], trc1, lb_s);
@@ -367,7 +375,7 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
         __syncthreads();
         const int chunk_next = s_ctl[1];
         // the block's sums -> global, then clear
-        const int KT = K * Tn;
+        const int KT = a.direct ? 0 : K * Tn;
         for (int idx = threadIdx.x; idx < KT; idx += blockDim.x) {
             const int k = idx / Tn, j = idx - k * Tn;
             const unsigned int l0 = s_acc[idx], l1 = s_acc[KT + idx], l2 = s_acc[2 * KT + idx], l3 = s_acc[3 * KT + idx];

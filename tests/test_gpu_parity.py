@@ -94,7 +94,8 @@ def test_c2_encode_holdout_fit_and_imputation(c2):
     assert abs(perf["f_measure"] - float(c2["f_measure"])) < 1e-6
 
 
-@pytest.mark.parametrize("n_basis,K", [(0, 2), (1, 3), (3, 3), (4, 5), (7, 2), (4, 10), (2, 17)])
+@pytest.mark.parametrize("n_basis,K", [(0, 2), (1, 3), (3, 3), (4, 5), (7, 2), (4, 10), (2, 17), (9, 3), (11, 4), (15, 2), (3, 40),
+                                       (4, 70)])
 def test_ragged_sparse_coverage_vs_oracle(n_basis, K):
     # low coverage => many uncovered (cell, region) pairs, ragged 1..20 CpGs per pair
     d, tr = synth.generate(48, 37, K, n_basis=n_basis, seed=11 + n_basis, sites_per_region=40,
@@ -287,8 +288,8 @@ def test_argument_errors_through_the_abi(c1):
     with mb.Engine(d, c1["basis"]) as eng:
         with pytest.raises(ValueError, match="shape"):
             eng.run(2, c1["w0_k3"], c1["k2_delta_0"])                       # w has K = 3 clusters
-        with pytest.raises(mb._lib.MelissaError, match="K must be in 1..64"):
-            eng.run(65, np.zeros((d.M, 4, 65)), np.full(65, 0.5))
+        with pytest.raises(mb._lib.MelissaError, match="K must be in 1..256"):
+            eng.run(257, np.zeros((d.M, 4, 257)), np.full(257, 0.5))
         with pytest.raises(mb._lib.MelissaError, match="delta_0 must be positive"):
             eng.run(2, c1["w0_k2"], np.array([0.5, -1.0]))
         with pytest.raises(mb._lib.MelissaError, match="vb_max_iter"):
@@ -299,8 +300,8 @@ def test_argument_errors_through_the_abi(c1):
     bad.y = bad.y.copy(); bad.y[5] = 2
     with pytest.raises(mb._lib.MelissaError, match="not 0/1"):
         mb.Engine(bad, c1["basis"])
-    with pytest.raises(mb._lib.MelissaError, match="0..7"):
-        mb.Engine(d, mb.create_rbf_object(9))
+    with pytest.raises(mb._lib.MelissaError, match="0..15"):
+        mb.Engine(d, mb.create_rbf_object(16))
 
 
 @pytest.mark.parametrize("case", ["K1", "M1", "single_cpg_pairs", "two_iterations", "one_cell_per_region_block"])
