@@ -39,11 +39,24 @@ typedef struct melissa_handle melissa_handle;
 #define MELISSA_FLAG_LB_DECREASED 1   /* warning("Warning: Lower bound decreases!")  R/melissa_vb.R:495-497 */
 #define MELISSA_FLAG_NOT_CONVERGED 2  /* warning("VB did not converge!")             R/melissa_vb.R:511-513 */
 
+#define MELISSA_FLAG_INTERRUPTED 4    /* the progress callback asked to stop (see melissa_set_progress) */
+
 /* basis kinds (BPRMeth basis objects; only the RBF object is pinned) */
 #define MELISSA_BASIS_RBF 1
 
 /* Message of the last failure on the calling thread ("" if none). */
 const char *melissa_last_error(void);
+
+/*
+ * Progress / interrupt hook: the role of the reference's progress bar and its message every 50th iteration
+ * (R/melissa_vb.R:305-307, :503-507), and the place where an R host checks for a user interrupt.  `fn` is called
+ * on the CALLING thread at every lower bound of a run started from that thread (melissa_vb_run,
+ * melissa_vb_run_multi) with the iteration, the bound and its change; a non-zero return stops the run after that
+ * iteration: the results so far are returned and MELISSA_FLAG_INTERRUPTED is set.  The callback must not longjmp
+ * (an R glue uses R_ToplevelExec around R_CheckUserInterrupt).  NULL removes the hook.
+ */
+typedef int (*melissa_progress_fn)(int32_t iteration, double lower_bound, double change, void *user);
+int melissa_set_progress(melissa_progress_fn fn, void *user);
 
 /* ABI version of the loaded library. */
 int melissa_abi_version(void);

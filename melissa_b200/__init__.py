@@ -8,12 +8,12 @@ libmelissa_b200.so (CUDA, sm_100a); there is no CPU fallback.
 """
 from . import _lib
 from .data import MelissaData, create_rbf_object, from_dict, from_nested, to_nested
-from .engine import Engine, MultiEngine, set_option
+from .engine import Engine, MultiEngine, progress, set_option
 from .evaluate import (cluster_ari, cluster_error, eval_cluster_performance, eval_imputation_performance,
                        impute_test_met)
 from .filters import filter_by_coverage_across_cells, filter_by_cpg_coverage, filter_by_variability
 from .vb import MelissaResult, finalize, melissa, melissa_inner, melissa_vb, shard_bounds, vb_loop
 
-__all__ = ["MelissaData", "create_rbf_object", "from_dict", "from_nested", "to_nested", "Engine", "MultiEngine", "set_option",
+__all__ = ["MelissaData", "create_rbf_object", "from_dict", "from_nested", "to_nested", "Engine", "MultiEngine", "progress", "set_option",
            "cluster_ari", "cluster_error", "eval_cluster_performance", "eval_imputation_performance", "impute_test_met",
            "filter_by_coverage_across_cells", "filter_by_cpg_coverage", "filter_by_variability", "MelissaResult", "finalize", "melissa", "melissa_inner", "melissa_vb", "shard_bounds", "vb_loop"]

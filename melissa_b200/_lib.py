@@ -14,10 +14,13 @@ c_i32, c_i64, c_dbl = C.c_int32, C.c_int64, C.c_double
 p_i32, p_i64, p_dbl, p_u8 = C.POINTER(c_i32), C.POINTER(c_i64), C.POINTER(c_dbl), C.POINTER(C.c_uint8)
 handle_t = C.c_void_p
 
+PROGRESS_FN = C.CFUNCTYPE(C.c_int, c_i32, c_dbl, c_dbl, C.c_void_p)
+
 # name -> (restype, argtypes); must list every symbol the header declares.
 SIGNATURES = {
     "melissa_last_error": (C.c_char_p, []),
     "melissa_abi_version": (C.c_int, []),
+    "melissa_set_progress": (C.c_int, [PROGRESS_FN, C.c_void_p]),
     "melissa_pack": (C.c_int, [c_i32, c_i32, c_i64, p_i64, p_i32, p_i32, p_dbl, p_u8, c_i32, c_i32, p_dbl, c_dbl,
                                c_i32, c_i32, C.POINTER(handle_t)]),
     "melissa_pack_device": (C.c_int, [c_i32, c_i32, c_i64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,

@@ -46,6 +46,8 @@
 namespace {
 
 thread_local std::string g_err;
+thread_local melissa_progress_fn g_progress = nullptr;      // melissa_set_progress: called at every bound of a run started
+thread_local void *g_progress_user = nullptr;               // from this thread
 
 int fail(int code, const char *fmt, ...) {
     char buf[1024];
@@ -1435,6 +1437,12 @@ __global__ void count_bad_y_kernel(const uint8_t *__restrict__ y, int64_t n, uns
 extern "C" {
 
 const char *melissa_last_error(void) { return g_err.c_str(); }
+
+int melissa_set_progress(melissa_progress_fn fn, void *user) {
+    g_progress = fn;
+    g_progress_user = user;
+    return MELISSA_OK;
+}
 int melissa_abi_version(void) { return 1; }
 
 static const char *pair_list_error(int code) {
@@ -2120,8 +2128,13 @@ int melissa_vb_run(melissa_handle *h, int32_t K, const double *w0, const double 
             ++nlb;
             if (v < lb_prev) fl |= MELISSA_FLAG_LB_DECREASED;               // :495-497
             const bool conv = std::fabs(v - lb_prev) < epsilon_conv;        // :499-501
+            const double diff = v - lb_prev;
             lb_prev = v;
             if (conv) break;
+            if (g_progress && g_progress(i, v, diff, g_progress_user)) {    // the host asks to stop (user interrupt)
+                fl |= MELISSA_FLAG_INTERRUPTED;
+                break;
+            }
         }
         if (i == vb_max_iter) fl |= MELISSA_FLAG_NOT_CONVERGED;             // :511-513
     }
@@ -2462,6 +2475,8 @@ int melissa_vb_run_multi(melissa_multi *mm, int32_t K, const double *w0, const d
     lbs.push_back(-std::numeric_limits<double>::infinity());        // LB <- c(-Inf), :242
     int fl = 0, it_last = 1;
     std::atomic<int> stop{0};
+    const melissa_progress_fn progress = g_progress;
+    void *const progress_user = g_progress_user;
     auto worker = [&](int g) {
         melissa_handle *h = mm->h[(size_t)g];
         PerGpu &me = pg[(size_t)g];
@@ -2528,6 +2543,10 @@ int melissa_vb_run_multi(melissa_multi *mm, int32_t K, const double *w0, const d
                     lbs.push_back(v);
                     if (v < prev) fl |= MELISSA_FLAG_LB_DECREASED;  // :495-497
                     if (std::fabs(v - prev) < epsilon_conv) stop.store(1);      // :499-501
+                    else if (progress && progress(i, v, v - prev, progress_user)) {       // (worker 0 IS the calling thread)
+                        fl |= MELISSA_FLAG_INTERRUPTED;
+                        stop.store(1);
+                    }
                     it_last = i;
                 }
                 if (!bar.wait()) return;
@@ -2545,7 +2564,8 @@ int melissa_vb_run_multi(melissa_multi *mm, int32_t K, const double *w0, const d
 #undef MG
     };
     std::vector<std::thread> th;
-    for (int g = 0; g < G; ++g) th.emplace_back(worker, g);
+    for (int g = 1; g < G; ++g) th.emplace_back(worker, g);
+    worker(0);                                                      // GPU 0 is driven by the caller's own thread
     for (auto &t : th) t.join();
     int rc = MELISSA_OK;
     for (int g = 0; g < G && !rc; ++g)

@@ -16,6 +16,21 @@ def set_option(key: str, value: int):
     _lib.check(_lib.load().melissa_set_option(key.encode(), int(value)))
 
 
+class progress:
+    """Context manager around melissa_set_progress: `fn(iteration, lower_bound, change)` is called at every bound of
+    the runs started inside the block; returning True stops the run (MELISSA_FLAG_INTERRUPTED)."""
+
+    def __init__(self, fn):
+        self._cb = _lib.PROGRESS_FN(lambda i, lb, diff, _user: 1 if fn(int(i), float(lb), float(diff)) else 0)
+
+    def __enter__(self):
+        _lib.check(_lib.load().melissa_set_progress(self._cb, None))
+        return self
+
+    def __exit__(self, *exc):
+        _lib.load().melissa_set_progress(None, None)
+
+
 class _DeviceBuffer:
     """Exposes a raw device pointer through __cuda_array_interface__ so torch can
     alias it (used only to hand the reduction buffers to torch.distributed)."""

@@ -15,6 +15,7 @@ from .engine import Engine
 
 FLAG_LB_DECREASED = 1
 FLAG_NOT_CONVERGED = 2
+FLAG_INTERRUPTED = 4
 
 
 class MelissaResult(dict):
@@ -144,7 +145,18 @@ def melissa(X, K=3, basis=None, delta_0=None, w=None, alpha_0=.5, beta_0=None, v
                                   vb_init_nstart, vb_init_max_iter, rng)
         else:
             optimal_w = np.asarray(w, np.float64)
-        obj = melissa_inner(eng, K, optimal_w, delta_0, alpha_0, beta_0, vb_max_iter, epsilon_conv)
+        if is_verbose:
+            # the reference's message every 50th iteration on which a bound was taken (R/melissa_vb.R:503-507)
+            from .engine import progress
+
+            def say(i, lb, diff):
+                if i % 50 == 0:
+                    print(f"\rIt:\t{i}\tLB:\t{lb}\tDiff:\t{diff}")
+                return False
+            with progress(say):
+                obj = melissa_inner(eng, K, optimal_w, delta_0, alpha_0, beta_0, vb_max_iter, epsilon_conv)
+        else:
+            obj = melissa_inner(eng, K, optimal_w, delta_0, alpha_0, beta_0, vb_max_iter, epsilon_conv)
     return finalize(obj, K, data.cell_names)
 
 

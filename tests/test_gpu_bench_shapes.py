@@ -159,3 +159,24 @@ def test_tma_staged_contraction_equals_the_plain_load_one():
     assert np.array_equal(out[0]["lb"], out[1]["lb"])
     assert np.array_equal(out[0]["W"], out[1]["W"])
     assert np.array_equal(out[0]["r_nk"], out[1]["r_nk"])
+
+
+def test_progress_hook_is_called_at_every_bound_and_can_stop_the_run(c1):
+    """melissa_set_progress: the reference's progress messages / the place for R_CheckUserInterrupt."""
+    seen = []
+    with mb.Engine(mb.from_dict(c1), c1["basis"]) as eng:
+        with mb.progress(lambda i, lb, diff: seen.append((i, lb)) or False):
+            full = eng.run(2, c1["w0_k2"], c1["k2_delta_0"], vb_max_iter=45, epsilon_conv=0.0)
+        assert [i for i, _ in seen] == [10, 20, 30, 40, 45] and full["flags"] & 4 == 0
+        np.testing.assert_array_equal([lb for _, lb in seen], full["lb"][1:])
+        with mb.progress(lambda i, lb, diff: i >= 20):
+            cut = eng.run(2, c1["w0_k2"], c1["k2_delta_0"], vb_max_iter=45, epsilon_conv=0.0)
+        assert cut["n_iter"] == 20 and cut["flags"] & 4 and np.array_equal(cut["lb"], full["lb"][:3])
+        after = eng.run(2, c1["w0_k2"], c1["k2_delta_0"], vb_max_iter=45, epsilon_conv=0.0)      # hook removed again
+        assert after["n_iter"] == 45
+    d = mb.from_dict(c1)
+    with mb.MultiEngine.pack(d, c1["basis"], 2, devices=[0, 0]) as me:
+        with mb.progress(lambda i, lb, diff: i >= 20):
+            cut2 = me.run(2, c1["w0_k2"], c1["k2_delta_0"], vb_max_iter=45, epsilon_conv=0.0)
+    assert cut2["n_iter"] == 20 and cut2["flags"] & 4
+    np.testing.assert_allclose(cut2["lb"][1:], cut["lb"][1:], rtol=1e-12)
