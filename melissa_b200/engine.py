@@ -28,7 +28,7 @@ class progress:
         return self
 
     def __exit__(self, *exc):
-        _lib.load().melissa_set_progress(None, None)
+        _lib.load().melissa_set_progress(_lib.PROGRESS_FN(), None)
 
 
 class _DeviceBuffer:
