@@ -1,9 +1,12 @@
 # Replacement for the body of Melissa:::melissa_inner (reference R/melissa_vb.R:232-529) that hands the
 # whole VB run to libmelissa_b200.so.  Written without an R installation at hand (see INTEGRATION.md).
 melissa_inner <- function(H, y, region_ind, cell_ind, K, basis, w, delta_0, alpha_0, beta_0,
-                          vb_max_iter, epsilon_conv, is_parallel, no_cores, is_verbose, X) {
+                          vb_max_iter, epsilon_conv, is_parallel, no_cores, is_verbose, X,
+                          n_gpus = getOption("melissa.n_gpus", 1L)) {
+  # n_gpus: GPUs of this box to shard the cells over (the role no_cores had for mclapply, R/utils.R:30-43)
   res <- .Call(C_melissa_fit, X, as.integer(K), as.integer(basis$M), as.numeric(basis$mus), basis$gamma,
-               w, delta_0, alpha_0, beta_0, as.integer(vb_max_iter), epsilon_conv)
+               w, delta_0, alpha_0, beta_0, as.integer(vb_max_iter), epsilon_conv, as.integer(n_gpus),
+               isTRUE(is_verbose))
   M <- dim(w)[1]; D <- dim(w)[2]
   S <- array(res[[2]], dim = c(D, D, M, K))                         # block (k, m) at ((k-1)*M + m-1)*D*D
   W_Sigma <- lapply(seq_len(K), function(k) lapply(seq_len(M), function(m) S[, , m, k]))
