@@ -231,6 +231,9 @@ int melissa_vb_fetch_HtEz(melissa_handle *h, double *out);
  * tree; parity with it is statistical)
  */
 int melissa_profiles_mle(melissa_handle *h, double lambda, int32_t n_iter, double *w_out);
+/* The same with w_out_device[P * D] in DEVICE memory on the handle's GPU, for a host that goes on clustering the
+ * profiles there (the k-means of the default initialisation, R/melissa_vb.R:147-169). */
+int melissa_profiles_mle_device(melissa_handle *h, double lambda, int32_t n_iter, double *w_out_device);
 
 /* Block until all work queued on the handle's stream is done. */
 int melissa_sync(melissa_handle *h);

@@ -51,6 +51,7 @@ SIGNATURES = {
     "melissa_vb_fetch": (C.c_int, [handle_t, p_dbl, p_dbl, p_dbl, p_dbl, p_dbl, p_dbl, p_dbl]),
     "melissa_vb_fetch_HtEz": (C.c_int, [handle_t, p_dbl]),
     "melissa_profiles_mle": (C.c_int, [handle_t, c_dbl, c_i32, p_dbl]),
+    "melissa_profiles_mle_device": (C.c_int, [handle_t, c_dbl, c_i32, C.c_void_p]),
     "melissa_sync": (C.c_int, [handle_t]),
     "melissa_launch_count": (c_i64, [handle_t]),
     "melissa_layout_info": (C.c_int, [handle_t, p_i64, c_i32]),

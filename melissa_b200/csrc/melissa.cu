@@ -1744,7 +1744,7 @@ int melissa_pack_device(int32_t n_cells, int32_t n_regions, int64_t n_pairs, con
                      gamma, device, allow_empty_regions, true, out);
 }
 
-int melissa_profiles_mle(melissa_handle *h, double lambda, int32_t n_iter, double *w_out) {
+static int profiles_mle_impl(melissa_handle *h, double lambda, int32_t n_iter, double *w_out, bool out_on_device) {
     if (!h) return fail(MELISSA_ERR_ARG, "handle is NULL");
     if (!w_out) return fail(MELISSA_ERR_ARG, "w_out is NULL");
     if (!(lambda >= 0.0) || n_iter < 1) return fail(MELISSA_ERR_ARG, "lambda >= 0 and n_iter >= 1 are required");
@@ -1768,17 +1768,26 @@ int melissa_profiles_mle(melissa_handle *h, double lambda, int32_t n_iter, doubl
         return MELISSA_OK;
     };
     if ((rc = run())) { cudaFree(d_out); return rc; }
-    double *d_pairs = nullptr;
-    if ((rc = dev_alloc(&d_pairs, h->P * D))) { cudaFree(d_out); return rc; }
+    double *d_pairs = out_on_device ? w_out : nullptr;
+    if (!out_on_device && (rc = dev_alloc(&d_pairs, h->P * D))) { cudaFree(d_out); return rc; }
     lanes_to_pairs_kernel<<<(unsigned)((sl->S * 32 + 255) / 256), 256, 0, h->stream>>>(d_out, sl->lane_pair, d_pairs,
                                                                                          sl->S * 32, D, h->R, 0);
     h->launches += 2;
-    cudaError_t e = cudaMemcpyAsync(w_out, d_pairs, (size_t)h->P * D * sizeof(double), cudaMemcpyDeviceToHost, h->stream);
+    cudaError_t e = cudaSuccess;
+    if (!out_on_device) e = cudaMemcpyAsync(w_out, d_pairs, (size_t)h->P * D * sizeof(double), cudaMemcpyDeviceToHost, h->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
     cudaFree(d_out);
-    cudaFree(d_pairs);
+    if (!out_on_device) cudaFree(d_pairs);
     if (e != cudaSuccess) return fail(MELISSA_ERR_CUDA, "melissa_profiles_mle failed: %s", cudaGetErrorString(e));
     return MELISSA_OK;
+}
+
+int melissa_profiles_mle(melissa_handle *h, double lambda, int32_t n_iter, double *w_out) {
+    return profiles_mle_impl(h, lambda, n_iter, w_out, false);
+}
+
+int melissa_profiles_mle_device(melissa_handle *h, double lambda, int32_t n_iter, double *w_out_device) {
+    return profiles_mle_impl(h, lambda, n_iter, w_out_device, true);
 }
 
 int melissa_set_option(const char *key, int64_t value) {

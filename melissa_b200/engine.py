@@ -181,6 +181,13 @@ class Engine:
         _lib.check(self.lib.melissa_profiles_mle(self.h, float(lam), int(n_iter), _lib.ptr(out, _lib.c_dbl)))
         return out
 
+    def profiles_mle_device(self, lam: float = 0.5, n_iter: int = 15):
+        """The same as a torch CUDA tensor [P, D] on the engine's GPU (melissa_profiles_mle_device)."""
+        import torch
+        out = torch.empty((self.P, self.D), dtype=torch.float64, device=f"cuda:{self.device}")
+        _lib.check(self.lib.melissa_profiles_mle_device(self.h, float(lam), int(n_iter), C.c_void_p(out.data_ptr())))
+        return out
+
     def sync(self):
         _lib.check(self.lib.melissa_sync(self.h))
 

@@ -2,9 +2,10 @@
 (reference R/melissa_vb.R:134-194): per-(cell, region) penalised probit MLE,
 k-means on the stacked profiles, `vb_init_nstart` short VB runs to rank the
 restarts.  The restarts run on the GPU through the same library call as the
-final fit, and so does the MLE (melissa_profiles_mle); k-means is host NumPy
-(parity here is statistical, the reference path depends on
-R's RNG, `optim` and `stats::kmeans`).
+final fit, and so does the MLE (melissa_profiles_mle_device); the profile
+matrix and Lloyd's k-means live on the GPU as torch tensors (SURVEY.md 8f rank 2:
+parity here is statistical, the reference path depends on R's RNG, `optim` and
+`stats::kmeans`).
 """
 from __future__ import annotations
 
@@ -14,21 +15,24 @@ import numpy as np
 
 
 
-def _kmeans(X, K, rng, n_iter=10):
-    """Plain Lloyd k-means, one random start (role of stats::kmeans(W_tmp, K, nstart = 1))."""
+def _kmeans(X, K, gen, n_iter=10):
+    """Plain Lloyd k-means on the GPU, one random start (role of stats::kmeans(W_tmp, K, nstart = 1)).
+    X: torch CUDA tensor [N, M D]; returns the labels as a CUDA tensor."""
+    import torch
     N = X.shape[0]
-    centres = X[rng.choice(N, K, replace=False)].copy()
-    lab = np.zeros(N, dtype=np.int64)
-    for _ in range(n_iter):
-        d2 = ((X * X).sum(1)[:, None] - 2.0 * X @ centres.T + (centres * centres).sum(1)[None])
+    centres = X[torch.randperm(N, generator=gen, device=X.device)[:K]].clone()
+    x2 = (X * X).sum(1)
+    lab = torch.zeros(N, dtype=torch.int64, device=X.device)
+    for it in range(n_iter):
+        d2 = x2[:, None] - 2.0 * (X @ centres.T) + (centres * centres).sum(1)[None]
         new = d2.argmin(1)
-        if np.array_equal(new, lab) and _ > 0:
+        if it > 0 and torch.equal(new, lab):
             break
         lab = new
-        for k in range(K):
-            sel = lab == k
-            if sel.any():
-                centres[k] = X[sel].mean(0)
+        sums = torch.zeros_like(centres).index_add_(0, lab, X)
+        cnt = torch.bincount(lab, minlength=K).to(X.dtype)
+        keep = cnt > 0
+        centres[keep] = sums[keep] / cnt[keep, None]
     return lab
 
 
@@ -36,25 +40,37 @@ def initial_w(engine, data, basis, K, delta_0, alpha_0, beta_0, epsilon_conv, is
               vb_init_nstart, vb_init_max_iter, rng):
     """R/melissa_vb.R:134-194.  Keeps the reference's two quirks: the restart
     whose mini-VB ends with the best lower bound contributes its INITIAL w
-    (:187-193), and vb_init_nstart == 1 skips the mini-VB (:174-177)."""
+    (:187-193), and vb_init_nstart == 1 skips the mini-VB (:174-177).
+    The per-pair MLE, the N x (M D) profile matrix and the k-means all stay on
+    the GPU; what comes back to the host are K profiles per restart."""
+    import torch
     N, M, D = data.N, data.M, int(basis["M"]) + 1
-    w_mle = engine.profiles_mle(0.5, 15)                 # GPU; no CPU path (hand-placed RBF centres: pass `w`)
-    ww = rng.normal(0.0, 0.01, size=(M, D, N))                               # :148
-    ww[data.pair_region, :, data.pair_cell] = w_mle                          # :151
-    W_tmp = ww.transpose(2, 1, 0).reshape(N, D * M)                          # c(ww[,,n]) column-major
+    dev = torch.device(f"cuda:{engine.device}")
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(int(rng.integers(0, 2 ** 62)))
+    w_mle = engine.profiles_mle_device(0.5, 15)          # [P, D] on the GPU; no CPU path (hand-placed centres: pass `w`)
+    X3 = 0.01 * torch.randn((N, D, M), generator=gen, device=dev, dtype=torch.float64)          # :148, as c(ww[,,n])
+    pc = torch.as_tensor(np.asarray(data.pair_cell), device=dev).long()
+    pr = torch.as_tensor(np.asarray(data.pair_region), device=dev).long()
+    X3[pc, :, pr] = w_mle                                                     # :151
+    del w_mle, pc, pr
+    W_tmp = X3.view(N, D * M)
+    profile = lambda n: X3[int(n)].T.cpu().numpy()                            # ww[, , n]: M x D
     lb_prev = -1e120
     optimal_w = None
     for _t in range(int(vb_init_nstart)):
         w = np.zeros((M, D, K))
         if is_kmeans:
-            lab = _kmeans(W_tmp, K, rng)
+            lab = _kmeans(W_tmp, K, gen)
             for k in range(K):
-                members = np.flatnonzero(lab == k)
-                if members.size == 0:                                        # the reference leaves this as a TODO (:165)
-                    members = np.arange(N)
-                w[:, :, k] = ww[:, :, rng.choice(members)]                   # :168
+                members = torch.nonzero(lab == k).flatten()
+                if members.numel() == 0:                                      # the reference leaves this as a TODO (:165)
+                    members = torch.arange(N, device=dev)
+                pick = members[torch.randint(members.numel(), (1,), generator=gen, device=dev)]
+                w[:, :, k] = profile(pick)                                    # :168
         else:
-            w = ww[:, :, rng.choice(N, K, replace=False)].copy()             # :171
+            for k, n in enumerate(torch.randperm(N, generator=gen, device=dev)[:K].tolist()):
+                w[:, :, k] = profile(n)                                       # :171
         if vb_init_nstart == 1:
             return w
         mini = engine.run(K, w, delta_0, alpha_0, beta_0, max(2, int(vb_init_max_iter)), epsilon_conv)
