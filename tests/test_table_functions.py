@@ -1,4 +1,4 @@
-"""CPU: the two table-driven special functions of the sweep (melissa_b200/csrc/sliced.cuh), restated
+"""CPU: the two table-driven special functions of the sweep (rbf_row3 / trunc_mean3, melissa_b200/csrc/sliced.cuh), restated
 operation by operation in NumPy and compared with mpmath at 40 digits.  This pins the table spacing
 and the series orders chosen there; the device code itself is covered by the GPU parity tests."""
 import math
@@ -12,11 +12,13 @@ mp.mp.dps = 40
 MAGIC = 6755399441055744.0
 
 
-def trunc_mean_table(t, sp=128, order=5):
+def trunc_mean_table(t, sp=512, order=4):
     """E[z | z > 0], z ~ N(t, 1): t + 1 / R(t), R = Phi / phi from a table at spacing 1/sp and the
-    recurrence c_{n+1} = (c_{n-1} + t0 c_n) / (n + 1) (trunc_mean_tab in sliced.cuh)."""
-    v = t * sp + MAGIC
-    t0 = (v - MAGIC) / sp
+    recurrence c_{n+1} = (c_{n-1} + t0 c_n) / (n + 1) (trunc_mean3 in sliced.cuh: the rounding constant carries the
+    scale and the table offset, the reciprocal is a 2^-23 seed plus one cubically convergent step)."""
+    magic = MAGIC / sp + 8.0                                            # MILLS_MAGIC
+    v = t + magic
+    t0 = v - magic
     d = t - t0
     R0 = math.sqrt(math.pi / 2) * erfcx(-t0 / math.sqrt(2))           # the table entry
     c = [R0, 1 + t0 * R0]
@@ -25,28 +27,48 @@ def trunc_mean_table(t, sp=128, order=5):
     R = c[order]
     for n in range(order - 1, -1, -1):
         R = R * d + c[n]
-    return t + 1.0 / R
+    y = (1.0 / R) * (1 + 2.0 ** -23)                                   # what MUFU.RCP64H guarantees
+    e = 1 - R * y
+    y = y * (e * e + e) + y
+    return t + y
 
 
-def rbf_row_table(x, M, sub=128):
-    """RBF row from the (E, B) table and the degree-7 / degree-6 series (eval_basis_tab in sliced.cuh)."""
+def rbf_table_log2(M):
+    """melissa.cu rbf_table_log2: grid spacing 2^-k with gamma s u_max <= 0.02 (series of order 6 / 5), 0.055 from
+    D = 10 on (order 8 / 7)."""
+    gamma, mu1 = M * M / 4.0, 2.0 / (M + 1) - 1.0
+    u_max = max(abs(-1 - mu1), abs(1 - mu1))
+    w_max = 0.02 if M + 1 <= 9 else 0.055
+    for k in range(8, 13):
+        if gamma * 2.0 ** -k * u_max <= w_max:
+            return k
+    raise AssertionError("gamma too large for the table")
+
+
+def rbf_row_table(x, M):
+    """RBF row from the (E, B) table on the grid x0 = j 2^-k and the short series in d = x - x0 (rbf_row3 in
+    sliced.cuh)."""
     gamma, delta = M * M / 4.0, 2.0 / (M + 1)
     mus = np.array([j * (2.0 / (M + 1)) - 1.0 for j in range(1, M + 1)])
-    s = delta / sub
-    u = x - mus[0]
-    v = u * (1.0 / s) + MAGIC
-    u0 = (v - MAGIC) * s
-    d = u - u0
+    k = rbf_table_log2(M)
+    s = 2.0 ** -k
+    nw = 6 if M + 1 <= 9 else 8
+    magic = (MAGIC + (2 ** k + 1)) * s
+    v = x + magic
+    x0 = v - magic
+    d = x - x0
+    u0 = x0 - mus[0]
     q = math.exp(-gamma * delta * delta)
     E, B = np.exp(-gamma * u0 * u0), q * np.exp(2 * gamma * delta * u0)  # the table entries (q folded into B)
-    w = (-gamma * d) * (2 * u0 + d)
-    c = np.full_like(w, 1.0 / 5040)
-    for k in (720, 120, 24, 6, 2, 1, 1):
-        c = c * w + 1.0 / k
+    w = d * (-gamma * d + (x0 * (-2 * gamma) + 2 * gamma * mus[0]))
+    fact = [1.0 / math.factorial(i) for i in range(10)]
+    c = np.full_like(w, fact[nw])
+    for i in range(nw - 1, -1, -1):
+        c = c * w + fact[i]
     z = 2 * gamma * delta * d
-    e = np.full_like(z, 1.0 / 720)
-    for k in (120, 24, 6, 2, 1, 1):
-        e = e * z + 1.0 / k
+    e = np.full_like(z, fact[nw - 1])
+    for i in range(nw - 2, -1, -1):
+        e = e * z + fact[i]
     h = [E * c]
     bj = B * e
     for _ in range(1, M):
@@ -68,7 +90,7 @@ def test_truncated_normal_mean_from_the_table_is_at_the_rounding_floor():
         assert rel.max() < 3 * max(rel_erf.max(), 2.3e-16)          # no worse than the closed form
 
 
-@pytest.mark.parametrize("M", [1, 3, 4, 7])
+@pytest.mark.parametrize("M", [1, 3, 4, 7, 9, 11, 15])
 def test_rbf_row_from_the_table_matches_direct_evaluation(M):
     rng = np.random.RandomState(M)
     x = rng.uniform(-1, 1, 1500)
@@ -79,4 +101,4 @@ def test_rbf_row_from_the_table_matches_direct_evaluation(M):
     err = (np.abs(H - ref) / ref).max()
     err_direct = (np.abs(direct - ref) / ref).max()
     assert err < 2 * err_direct + 1e-15, (err, err_direct)      # as accurate as calling exp on the rounded argument
-    assert err < 1e-14
+    assert err < 1e-14 if M <= 8 else err < 5e-14               # (the error of both grows with gamma (x - mu)^2)
