@@ -904,7 +904,7 @@ void free_sliced(melissa_handle *h) {
     cudaFree(sl->x_sell); cudaFree(sl->ybits); cudaFree(sl->slice_xbase); cudaFree(sl->slice_ybase);
     cudaFree(sl->slice_len); cudaFree(sl->slice_region); cudaFree(sl->slice_cb); cudaFree(sl->lane_cell);
     cudaFree(sl->lane_meta); cudaFree(sl->lane_pair); cudaFree(sl->blk_cells); cudaFree(sl->reg_slice_ptr);
-    cudaFree(sl->reg_slice); cudaFree(sl->stats); cudaFree(sl->mills_tab); cudaFree(sl->rbf_tab);
+    cudaFree(sl->reg_slice); cudaFree(sl->stats); cudaFree(sl->mills_tab); cudaFree(sl->lphi_tab); cudaFree(sl->rbf_tab);
     cudaFree(sl->chunk_ptr); cudaFree(sl->chunk_counter);
     delete sl;
     h->sl = nullptr;
@@ -1118,7 +1118,7 @@ int finish_sliced(melissa_handle *h, Sliced *sl, int64_t *d_src, cudaStream_t st
     if ((rc = upload(&sl->rbf_tab, rbf_tab))) { cudaFree(d_src); return rc; }
     // slack: the sweep's x ring reads up to NST groups past the end of a slice
     if ((rc = dev_alloc(&sl->x_sell, sl->x_len + 2 * SWEEP3_NST * SWEEP3_XU * 32)) || (rc = dev_alloc(&sl->ybits, sl->y_len)) ||
-        (rc = dev_alloc(&sl->stats, S * h->R * 32)) || (rc = dev_alloc(&sl->mills_tab, MILLS_N)) ||
+        (rc = dev_alloc(&sl->stats, S * h->R * 32)) || (rc = dev_alloc(&sl->mills_tab, MILLS_N)) || (rc = dev_alloc(&sl->lphi_tab, MILLS_N)) ||
         (rc = dev_alloc(&sl->chunk_counter, 1))) {
         cudaFree(d_src);
         return rc;
@@ -1137,7 +1137,8 @@ int finish_sliced(melissa_handle *h, Sliced *sl, int64_t *d_src, cudaStream_t st
         if ((rc = run())) { cudaFree(d_src); return rc; }
     }
     mills_table_kernel<<<(MILLS_N + 255) / 256, 256, 0, st>>>(sl->mills_tab);
-    h->launches += 3;
+    lphi_table_kernel<<<(MILLS_N + 255) / 256, 256, 0, st>>>(sl->lphi_tab);
+    h->launches += 4;
     const cudaError_t e = cudaStreamSynchronize(st);
     cudaFree(d_src);
     if (e != cudaSuccess) return fail(MELISSA_ERR_CUDA, "sliced layout build failed: %s", cudaGetErrorString(e));
@@ -1327,7 +1328,7 @@ int launch_sweep3(melissa_handle *h, bool with_lb) {
     a.lane_cell = sl->lane_cell; a.lane_meta = sl->lane_meta; a.blk_cells = sl->blk_cells;
     a.chunk_ptr = sl->chunk_ptr; a.stats = sl->stats; a.U = h->U; a.r = h->r;
     a.log_rho_fx = h->log_rho_fx; a.lb_fx = h->lb_fx; a.poison = h->poison;
-    a.mills_tab = sl->mills_tab; a.rbf_tab = sl->rbf_tab; a.rt = sl->rt; a.basis = h->basis;
+    a.mills_tab = sl->mills_tab; a.lphi_tab = sl->lphi_tab; a.rbf_tab = sl->rbf_tab; a.rt = sl->rt; a.basis = h->basis;
     a.K = h->K; a.Tn = sl->Tn; a.NC = sl->NC; a.G = std::max(1, g_opt_sweep_group);
     a.chunk_counter = sl->chunk_counter;
     const int block = 32 * nw;
@@ -1353,6 +1354,7 @@ int launch_sweep3(melissa_handle *h, bool with_lb) {
 
 int g_opt_contract_mma = 1;
 int g_opt_contract_tma = 1;
+int g_opt_contract_warps = 0;     // 0 = chosen from the slices per region
 
 template <int MT, int NT>
 int launch_contract_mma_t(melissa_handle *h, int block) {
@@ -1388,6 +1390,7 @@ int launch_contract_v2(melissa_handle *h) {
         const int64_t avg_slices = std::max<int64_t>(1, sl->S / std::max(1, h->M));
         int nw = 8;
         while (nw > 1 && avg_slices / nw < 4) nw >>= 1;
+        if (g_opt_contract_warps > 0) nw = std::min(8, g_opt_contract_warps);
         const int block = 32 * nw;
         int rc = MELISSA_OK;
         // operand staged by the bulk-copy engine (contract_tma.cuh) unless switched off ("contract_tma" option)
@@ -1827,6 +1830,11 @@ int melissa_set_option(const char *key, int64_t value) {
     }
     if (!std::strcmp(key, "contract_tma")) {
         g_opt_contract_tma = value != 0;
+        return MELISSA_OK;
+    }
+    if (!std::strcmp(key, "contract_warps")) {
+        if (value < 0 || value > 8) return fail(MELISSA_ERR_ARG, "contract_warps must be in 0..8 (0 = automatic)");
+        g_opt_contract_warps = (int)value;
         return MELISSA_OK;
     }
     if (!std::strcmp(key, "sliced")) {

@@ -49,6 +49,7 @@ struct Sliced {
     int32_t *reg_slice = nullptr;         // [S]
     double *stats = nullptr;              // [S][8][R][4]
     double *mills_tab = nullptr;          // [MILLS_N]
+    double2 *lphi_tab = nullptr;          // [MILLS_N] (L, L') of L(t) = log(Phi(t) + 1e-10) on the same grid
     double2 *rbf_tab = nullptr;           // [rt.n_entries] (E(u0), q B(u0))
     RbfTab rt{};
     int32_t *chunk_ptr = nullptr;         // [NC + 1] first slice of each chunk of the sweep
@@ -67,6 +68,17 @@ __global__ void mills_table_kernel(double *tab) {
     tab[i] = R;
 }
 
+// L(t0) = log(Phi(t0) + 1e-10) and q(t0) = L'(t0) = phi / (Phi + 1e-10) on the same grid.  q obeys q' = -q (t + q)
+// whatever the constant next to Phi is, so the sweep gets every further Taylor coefficient of L from these two.
+__global__ void lphi_table_kernel(double2 *tab) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= MILLS_N) return;
+    const double t0 = (double)(i - MILLS_HALF) / (double)MILLS_SP;
+    const double Phi = 0.5 * erfc(-t0 * 0.70710678118654752440);
+    const double phi = 0.39894228040143267794 * exp(-0.5 * t0 * t0);
+    tab[i] = make_double2(log(Phi + 1e-10), phi / (Phi + 1e-10));
+}
+
 // Series coefficients that are not exactly representable in a 32-bit immediate live in
 // constant memory: a DFMA can take one operand straight from the constant bank, whereas a
 // literal costs two register moves every time the (register-starved) loop needs it again.
@@ -74,6 +86,22 @@ __constant__ double kInvIntC[7] = {0.0, 1.0, 0.5, 1.0 / 3, 0.25, 0.2, 1.0 / 6};
 #define kInvInt(i) kInvIntC[i]
 __constant__ double kInvFact3[10] = {1.0, 1.0, 0.5, 1.0 / 6, 1.0 / 24, 1.0 / 120, 1.0 / 720, 1.0 / 5040, 1.0 / 40320,
                                      1.0 / 362880};
+
+// log(Phi(t) + 1e-10) at t = t0 + dt, |dt| <= 1 / (2 MILLS_SP), from the table entry (L0, a0) of t0:
+//   L = L0 + a0 dt + a1 dt^2 / 2 + a2 dt^3 / 3 + a3 dt^4 / 4,   (n + 1) a_{n+1} = -(t0 a_n + a_{n-1}) - sum_i a_i a_{n-i}
+// (the Taylor coefficients of q = L' about t0).  The first term left out is a4 dt^5 / 5 with dt^5 / 5 <= 1.8e-16.
+__device__ __forceinline__ double log_phi_eps(double t0, double dt, double2 e) {
+    const double a0 = e.y;
+    const double s2 = fma(2.0, a0, t0);
+    const double a1 = -a0 * (t0 + a0);
+    const double a2 = -0.5 * fma(a1, s2, a0);
+    const double a3 = -kInvInt(3) * fma(a2, s2, fma(a1, a1, a1));
+    double p = fma(dt, 0.25 * a3, kInvInt(3) * a2);
+    p = fma(dt, p, 0.5 * a1);
+    p = fma(dt, p, a0);
+    return fma(dt, p, e.x);
+}
+
 
 template <int N>
 __device__ __forceinline__ double exp_series(double w) {         // sum_{i <= N} w^i / i!

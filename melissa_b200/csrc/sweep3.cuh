@@ -30,6 +30,7 @@ struct Sweep3Args {
     unsigned long long *lb_fx;                // [4]: lb_pz_qz (lo, hi), #CpG with s mu < -5, unused
     unsigned int *poison;                     // set when a term is non-finite or beyond the fixed-point range
     const double *mills_tab;
+    const double2 *lphi_tab;
     const double2 *rbf_tab;
     RbfTab rt;
     BasisDev basis;
@@ -291,9 +292,10 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
 #pragma unroll
                                 for (int d = 1; d < D; ++d) g[d] = fma(h[d], Ez, g[d]);
                                 if (WITH_LB) {
-                                    // log(Phi(s mu) + 1e-10): both branches of R/melissa_vb.R:471-472 reduce to it, and
-                                    // Phi = R * phi with the R the E[z] evaluation just produced (one exp + one log)
-                                    lb_s += fma(0.5 * mu, mu, log(fma(Rt, 0.39894228040143267794 * exp(-0.5 * t * t), 1e-10)));
+                                    // log(Phi(s mu) + 1e-10): both branches of R/melissa_vb.R:471-472 reduce to it; taken
+                                    // from its own table on the grid point t0 the E[z] evaluation just used (the table
+                                    // is read through L1 / L2: this branch runs on bound iterations only)
+                                    lb_s += fma(0.5 * mu, mu, log_phi_eps(t0, dt, __ldg(a.lphi_tab + ic)));
                                     wrong_s += t < -5.0;
                                 }
                             }

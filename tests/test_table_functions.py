@@ -33,6 +33,26 @@ def trunc_mean_table(t, sp=512, order=4):
     return t + y
 
 
+def log_phi_eps_table(t, sp=512):
+    """log(Phi(t) + 1e-10) from the (L, L') table at spacing 1/sp and the recurrence of q = L', q' = -q (t + q)
+    (log_phi_eps in sliced.cuh), operation by operation."""
+    magic = MAGIC / sp + 8.0
+    v = t + magic
+    t0 = v - magic
+    d = t - t0
+    Phi0 = mp.ncdf(t0)
+    L0 = float(mp.log(Phi0 + mp.mpf("1e-10")))                          # the table entry, correctly rounded
+    a0 = float(mp.npdf(t0) / (Phi0 + mp.mpf("1e-10")))
+    s2 = 2.0 * a0 + t0
+    a1 = -a0 * (t0 + a0)
+    a2 = -0.5 * (a1 * s2 + a0)
+    a3 = -(1.0 / 3) * (a2 * s2 + (a1 * a1 + a1))
+    p = d * (0.25 * a3) + (1.0 / 3) * a2
+    p = d * p + 0.5 * a1
+    p = d * p + a0
+    return d * p + L0
+
+
 def rbf_table_log2(M):
     """melissa.cu rbf_table_log2: grid spacing 2^-k with gamma s u_max <= 0.02 (series of order 6 / 5), 0.055 from
     D = 10 on (order 8 / 7)."""
@@ -88,6 +108,20 @@ def test_truncated_normal_mean_from_the_table_is_at_the_rounding_floor():
         rel_erf = np.abs(erf - ref) / np.abs(ref)
         assert rel.max() < tol, (lo, hi, rel.max())
         assert rel.max() < 3 * max(rel_erf.max(), 2.3e-16)          # no worse than the closed form
+
+
+def test_log_phi_from_the_table_is_at_the_rounding_floor():
+    """The bound's per-CpG term log(Phi(t) + 1e-10) (R/melissa_vb.R:471-472): absolute error against 40-digit
+    arithmetic, everywhere on the table including the stretch around t = -6.4 where the 1e-10 takes over."""
+    rng = np.random.default_rng(5)
+    ts = np.concatenate([rng.uniform(-7.99, 7.99, 4000), rng.uniform(-6.8, -6.0, 1000),
+                         (np.arange(-4090, 4090, 37) + 0.4999) / 512.0])
+    worst = 0.0
+    for t in ts:
+        want = mp.log(mp.ncdf(mp.mpf(float(t))) + mp.mpf("1e-10"))
+        got = log_phi_eps_table(float(t))
+        worst = max(worst, abs(float(got - want)) / max(1.0, abs(float(want))))
+    assert worst < 1e-15, worst                       # a few ulp of a term that is -3 ... -23 there
 
 
 @pytest.mark.parametrize("M", [1, 3, 4, 7, 9, 11, 15])
