@@ -250,7 +250,7 @@ def run_single_process(args, wl, config):
             t0 = time.perf_counter()
             with mb.MultiEngine.pack(hd, tr["basis"], G) as me2:
                 o2 = me2.run(K, tr["w0"], delta_0, vb_max_iter=steps + 1, epsilon_conv=0.0, lb_every=LB_EVERY)
-            dt = time.perf_counter() - t0
+                dt = time.perf_counter() - t0              # (the one-GPU arm also stops its clock before the free)
             h2d = hp.numel() * 8 + hc.numel() * 4 + hr.numel() * 4 + hx.numel() * 8 + hy.numel() + tr["w0"].nbytes
             d2h = sum(np.asarray(o2[k]).nbytes for k in ("W", "W_Sigma", "r_nk", "delta", "beta", "pi_k"))
             e2e = dict(value=P_tot * steps / dt, unit=UNIT, h2d_bytes_per_step=h2d / steps, d2h_bytes_per_step=d2h / steps, seconds=dt,

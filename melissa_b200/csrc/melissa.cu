@@ -687,6 +687,17 @@ struct StageTimer {       // MELISSA_PACK_TIMING=1 prints where melissa_pack spe
     }
 };
 
+struct HostLap {          // MELISSA_PACK_TIMING set: host-clock laps of the multi-GPU entry points (no device sync)
+    bool on = std::getenv("MELISSA_PACK_TIMING") != nullptr;
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    void lap(const char *what) {
+        if (!on) return;
+        const auto t1 = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[melissa_multi] %-28s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
+    }
+};
+
 // library-wide options (melissa_set_option)
 int g_opt_cell_block = 0;     // 0 = 256 cells
 int g_opt_sliced = -1;        // -1 auto, 0 never, 1 require
@@ -1131,7 +1142,7 @@ int finish_sliced(melissa_handle *h, Sliced *sl, int64_t *d_src, cudaStream_t st
     {
         auto run = [&]() -> int {
             DISPATCH_D(h->D, hh_sliced_kernel<DD><<<grid, 256, 0, st>>>(sl->x_sell, sl->slice_xbase, sl->lane_meta, sl->stats,
-                                                                S, h->basis));
+                                                                S, h->basis, sl->rt, sl->rbf_tab));
             return MELISSA_OK;
         };
         if ((rc = run())) { cudaFree(d_src); return rc; }
@@ -1388,7 +1399,9 @@ int launch_contract_v2(melissa_handle *h) {
     if (g_opt_contract_mma && MT <= 4 && NT <= 6) {
         // warps per region: enough to keep >= ~32 warps per SM in flight, not more than the region has slices
         const int64_t avg_slices = std::max<int64_t>(1, sl->S / std::max(1, h->M));
-        int nw = 8;
+        // (a region with few slices -- a small shard -- is spread over fewer warps so that more CTAs share an SM and
+        // their start-up and final cross-warp sums overlap: 0.370 -> 0.344 ms on an eighth of C4)
+        int nw = avg_slices < 128 ? 4 : 8;
         while (nw > 1 && avg_slices / nw < 4) nw >>= 1;
         if (g_opt_contract_warps > 0) nw = std::min(8, g_opt_contract_warps);
         const int block = 32 * nw;
@@ -1462,7 +1475,9 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
                      const int32_t *pair_cell_in, const int32_t *pair_region_in, const double *x,
                      const uint8_t *y, int32_t basis_kind, int32_t n_basis, const double *mus,
                      double gamma, int32_t device, int32_t allow_empty_regions, bool on_device,
-                     melissa_handle **out) {
+                     melissa_handle **out, int64_t ptr_base = 0, int32_t cell_base = 0) {
+    // ptr_base / cell_base: the lists are a window of a larger job's lists (melissa_pack_multi): offsets start at
+    // ptr_base instead of 0 and cells at cell_base; x and y already point at the window's first CpG
     if (!out) return fail(MELISSA_ERR_ARG, "out is NULL");
     StageTimer tm_pack;
     *out = nullptr;
@@ -1503,12 +1518,26 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
         pair_cell = host_cell.data();
         pair_region = host_region.data();
     }
+    std::vector<int64_t> rb_ptr;
+    std::vector<int32_t> rb_cell;
+    if ((ptr_base != 0 || cell_base != 0) && (host_build || on_device)) {
+        // the host builders want plain lists: make them (the device path below rebases after the upload instead)
+        if (on_device) return fail(MELISSA_ERR_ARG, "a window of device-resident lists is not supported");
+        rb_ptr.resize((size_t)P + 1);
+        rb_cell.resize((size_t)P);
+        for (int64_t p = 0; p <= P; ++p) rb_ptr[(size_t)p] = pair_ptr_in[p] - ptr_base;
+        for (int64_t p = 0; p < P; ++p) rb_cell[(size_t)p] = pair_cell_in[p] - cell_base;
+        pair_ptr = pair_ptr_in = rb_ptr.data();
+        pair_cell = pair_cell_in = rb_cell.data();
+        ptr_base = 0;
+        cell_base = 0;
+    }
     const bool have_host_lists = !on_device || host_build;
     std::vector<int64_t> reg_cnt((size_t)n_regions + 1, 0);
     int64_t nnz = 0;
     if (have_host_lists) {
     // ---- validate the pair list on the host (before the first CUDA call when the lists are host memory)
-    if (pair_ptr[0] != 0) return fail(MELISSA_ERR_ARG, "pair_ptr[0] must be 0");
+    if (pair_ptr[0] != ptr_base) return fail(MELISSA_ERR_ARG, "pair_ptr[0] must be 0");
     {
         // every rule relates pair p to pair p-1 only, so chunks are checked by separate host threads;
         // the failure with the lowest pair index is the one reported
@@ -1522,11 +1551,11 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
             std::vector<int64_t> &c = cnt[(size_t)t];
             c.assign((size_t)n_regions, 0);
             for (int64_t p = lo; p < hi; ++p) {
-                const int32_t n = pair_cell[p], m = pair_region[p];
+                const int32_t n = pair_cell[p] - cell_base, m = pair_region[p];
                 int code = 0;
                 if (n < 0 || n >= n_cells || m < 0 || m >= n_regions) code = 1;
                 else {
-                    const int32_t pn = p ? pair_cell[p - 1] : -1, pm = p ? pair_region[p - 1] : -1;
+                    const int32_t pn = p ? pair_cell[p - 1] - cell_base : -1, pm = p ? pair_region[p - 1] : -1;
                     if (n < pn) code = 2;
                     else if (n > pn + 1) code = 3;
                     else if (n == pn && m <= pm) code = 4;
@@ -1551,19 +1580,19 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
                 case 1: return fail(MELISSA_ERR_ARG, "pair %lld: cell/region index out of range", p);
                 case 2: return fail(MELISSA_ERR_ARG, "pairs must be cell-major (pair %lld)", p);
                 case 3: return fail(MELISSA_ERR_ARG, "cell %d: No coverage across all regions. This cell should be discarded!",
-                                    (b.p ? pair_cell[b.p - 1] : -1) + 1);
+                                    (b.p ? pair_cell[b.p - 1] : cell_base - 1) + 1);
                 case 4: return fail(MELISSA_ERR_ARG, "regions must be strictly increasing inside a cell (pair %lld)", p);
                 case 5: return fail(MELISSA_ERR_ARG, "pair %lld has no CpG", p);
                 default: return fail(MELISSA_ERR_ARG, "pair %lld has more than 65535 CpGs", p);
             }
         }
-        if (pair_cell[P - 1] != n_cells - 1)
+        if (pair_cell[P - 1] - cell_base != n_cells - 1)
             return fail(MELISSA_ERR_ARG, "cell %d: No coverage across all regions. This cell should be discarded!",
                         pair_cell[P - 1] + 1);
         for (int t = 0; t < nthr; ++t)
             for (int32_t m = 0; m < n_regions; ++m) reg_cnt[(size_t)m + 1] += cnt[(size_t)t][(size_t)m];
     }
-    nnz = pair_ptr[P];
+    nnz = pair_ptr[P] - ptr_base;
     if (!allow_empty_regions)
         for (int32_t m = 0; m < n_regions; ++m)
             if (reg_cnt[(size_t)m + 1] == 0)
@@ -1625,6 +1654,8 @@ static int pack_impl(int32_t n_cells, int32_t n_regions, int64_t n_pairs, const 
             PK(cudaMemcpyAsync(d_ptr, pair_ptr_in, (size_t)(P + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, sc));
             PK(cudaMemcpyAsync(d_cell, pair_cell_in, (size_t)P * sizeof(int32_t), cudaMemcpyHostToDevice, sc));
             PK(cudaMemcpyAsync(d_reg, pair_region_in, (size_t)P * sizeof(int32_t), cudaMemcpyHostToDevice, sc));
+            if (ptr_base != 0 || cell_base != 0)
+                pk_rebase_kernel<<<grid_for(P + 1, 256, h->sm_count, 8), 256, 0, sc>>>(d_ptr, d_cell, P, ptr_base, cell_base);
         }
     }
     PK(cudaEventRecord(e_idx, sc));
@@ -2386,9 +2417,11 @@ int melissa_multi_create(int32_t n_gpus, melissa_handle **handles, melissa_multi
 
 int melissa_multi_free(melissa_multi *mm) {
     if (!mm) return MELISSA_OK;
+    HostLap tm;
     if (mm->own_handles)
         for (melissa_handle *h : mm->h) melissa_free(h);
     delete mm;
+    tm.lap("free");
     return MELISSA_OK;
 }
 
@@ -2419,6 +2452,7 @@ int melissa_pack_multi(int32_t n_cells, int32_t n_regions, int64_t n_pairs, cons
         return MELISSA_OK;
     }
     // contiguous cell ranges balanced by CpG count (coverage varies several-fold across cells)
+    HostLap tm;
     const int64_t P = n_pairs;
     if (pair_ptr[0] != 0) return fail(MELISSA_ERR_ARG, "pair_ptr[0] must be 0");
     std::vector<int64_t> cell_first((size_t)n_cells + 1);
@@ -2436,6 +2470,7 @@ int melissa_pack_multi(int32_t n_cells, int32_t n_regions, int64_t n_pairs, cons
         }
         bound[(size_t)g] = std::max(bound[(size_t)g - 1] + 1, std::min(b, n_cells - (n_gpus - g)));
     }
+    tm.lap("pack_multi: shard bounds");
     std::vector<melissa_handle *> hs((size_t)n_gpus, nullptr);
     std::vector<int> rcs((size_t)n_gpus, MELISSA_OK);
     std::vector<std::string> errs((size_t)n_gpus);
@@ -2444,15 +2479,13 @@ int melissa_pack_multi(int32_t n_cells, int32_t n_regions, int64_t n_pairs, cons
         th.emplace_back([&, g]() {
             const int c0 = bound[(size_t)g], c1 = bound[(size_t)g + 1];
             const int64_t p0 = cell_first[(size_t)c0], p1 = cell_first[(size_t)c1], i0 = pair_ptr[p0];
-            std::vector<int64_t> ptr((size_t)(p1 - p0) + 1);
-            std::vector<int32_t> cell((size_t)(p1 - p0));
-            for (int64_t p = p0; p <= p1; ++p) ptr[(size_t)(p - p0)] = pair_ptr[p] - i0;
-            for (int64_t p = p0; p < p1; ++p) cell[(size_t)(p - p0)] = pair_cell[p] - c0;
-            rcs[(size_t)g] = melissa_pack(c1 - c0, n_regions, p1 - p0, ptr.data(), cell.data(), pair_region + p0, x + i0, y + i0,
-                                          basis_kind, n_basis, mus, gamma, devices ? devices[g] : g, 1, &hs[(size_t)g]);
+            // the shard is a window of the caller's lists: no host copy, the offsets are taken off on the device
+            rcs[(size_t)g] = pack_impl(c1 - c0, n_regions, p1 - p0, pair_ptr + p0, pair_cell + p0, pair_region + p0, x + i0, y + i0,
+                                       basis_kind, n_basis, mus, gamma, devices ? devices[g] : g, 1, false, &hs[(size_t)g], i0, c0);
             if (rcs[(size_t)g]) errs[(size_t)g] = g_err;
         });
     for (auto &t : th) t.join();
+    tm.lap("pack_multi: shards packed");
     for (int g = 0; g < n_gpus; ++g)
         if (rcs[(size_t)g]) {
             for (melissa_handle *h : hs) melissa_free(h);
@@ -2485,6 +2518,7 @@ int melissa_vb_run_multi(melissa_multi *mm, int32_t K, const double *w0, const d
         std::string err;
     };
     std::vector<PerGpu> pg((size_t)G);
+    HostLap tm;
     HostBarrier bar;
     bar.n = G;
     // shared between the host threads (written by thread 0 between two barriers)
@@ -2520,6 +2554,7 @@ int melissa_vb_run_multi(melissa_multi *mm, int32_t K, const double *w0, const d
         MG(cudaEventCreate(&me.ev_t1));
         MG(cudaStreamSynchronize(me.st));                           // set-up and the first sweep are not part of the loop
         if (!bar.wait()) return;                                    // everybody's buffers and events exist
+        if (g == 0) tm.lap("run_multi: begin + 1st sweep");
         MG(cudaEventRecord(me.ev_t0, me.st));
         for (int i = 2; i <= vb_max_iter; ++i) {                    // :309
             const int par = i & 1;
@@ -2584,6 +2619,7 @@ int melissa_vb_run_multi(melissa_multi *mm, int32_t K, const double *w0, const d
     for (int g = 1; g < G; ++g) th.emplace_back(worker, g);
     worker(0);                                                      // GPU 0 is driven by the caller's own thread
     for (auto &t : th) t.join();
+    tm.lap("run_multi: loop");
     int rc = MELISSA_OK;
     for (int g = 0; g < G && !rc; ++g)
         if (pg[(size_t)g].rc) rc = fail(pg[(size_t)g].rc, "%s", pg[(size_t)g].err.c_str());
@@ -2602,6 +2638,7 @@ int melissa_vb_run_multi(melissa_multi *mm, int32_t K, const double *w0, const d
             }
         }
     }
+    tm.lap("run_multi: fetch");
     // ---- put the handles back the way melissa_vb_begin left them, release the per-run resources
     for (int g = 0; g < G; ++g) {
         melissa_handle *h = mm->h[(size_t)g];

@@ -18,6 +18,15 @@
 constexpr int PK_J_BITS = 12, PK_LEN_BITS = 16, PK_REG_BITS = 20;      // key fields, low to high; the block id takes the rest
 constexpr int PK_GROUP_SHIFT = PK_J_BITS + PK_LEN_BITS;                // key >> this = (block, region)
 
+// A shard's lists as a window of a larger job's lists: offsets and cell numbers made local after the upload.
+__global__ void pk_rebase_kernel(int64_t *__restrict__ pair_ptr, int32_t *__restrict__ pair_cell, int64_t P, int64_t ptr_base,
+                                 int32_t cell_base) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i <= P; i += (int64_t)gridDim.x * blockDim.x) {
+        pair_ptr[i] -= ptr_base;
+        if (i < P) pair_cell[i] -= cell_base;
+    }
+}
+
 __global__ void pk_validate_kernel(const int64_t *__restrict__ pair_ptr, const int32_t *__restrict__ pair_cell,
                                    const int32_t *__restrict__ pair_region, int64_t P, int n_cells, int n_regions,
                                    unsigned long long *first_bad, int *reg_seen) {

@@ -219,7 +219,7 @@ sell_fill_kernel(const double *__restrict__ x, const uint8_t *__restrict__ y, co
 template <int D>
 __global__ void hh_sliced_kernel(const double *__restrict__ x_sell, const int64_t *__restrict__ slice_xbase,
                                  const int32_t *__restrict__ lane_meta, double *__restrict__ stats, int64_t S,
-                                 BasisDev basis) {
+                                 BasisDev basis, RbfTab rt, const double2 *__restrict__ rbf_tab) {
     constexpr int T = D * (D + 1) / 2, R = D + T;
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= S * 32) return;
@@ -231,8 +231,12 @@ __global__ void hh_sliced_kernel(const double *__restrict__ x_sell, const int64_
 #pragma unroll
     for (int q = 0; q < T; ++q) hh[q] = 0.0;
     for (int i = 0; i < len; ++i) {
+        // the same table-driven row the sweep uses (the table sits in L1 here); exp() for a position off the table
         double h[D];
-        eval_basis<D>(x_sell[xb + (int64_t)i * 32 + lane], basis, h);
+        const double x = x_sell[xb + (int64_t)i * 32 + lane];
+        unsigned bad = 0;
+        rbf_row3<D>(x, rt, rbf_tab, h, bad);
+        if (bad) eval_basis<D>(x, basis, h);
         int q = 0;
 #pragma unroll
         for (int a = 0; a < D; ++a)

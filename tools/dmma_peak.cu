@@ -8,7 +8,7 @@ __device__ __forceinline__ void dmma(double &c0, double &c1, double a, double b)
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
-// MODE 0: 8 independent DMMA chains; 1: 8 independent DFMA chains; 2: DMMA + NI integer ops per DMMA; 3: DFMA + NI integer
+// MODE 5 / 6: DFMA + NI LOP3 per DFMA / LOP3 only.  MODE 0: 8 independent DMMA chains; 1: 8 independent DFMA chains; 2: DMMA + NI integer ops per DMMA; 3: DFMA + NI integer
 // ops per DFMA; 4: integer ops only (NI per slot)
 template <int MODE, int NI>
 __global__ void k(double *out, int iters, double seed) {
@@ -20,10 +20,13 @@ __global__ void k(double *out, int iters, double seed) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             if (MODE == 0 || MODE == 2) dmma(c[i][0], c[i][1], a, b);
-            if (MODE == 1 || MODE == 3) f[i] = fma(f[i], a, b);
-            if (MODE >= 2) {
+            if (MODE == 1 || MODE == 3 || MODE == 5) f[i] = fma(f[i], a, b);
+            if (MODE == 5 || MODE == 6) {                                  // full-rate integer work: one LOP3 per statement
 #pragma unroll
-                for (int j = 0; j < NI; ++j) z[i] = z[i] * 1664525u + 1013904223u;
+                for (int j = 0; j < NI; ++j) z[(i + j) & 7] = (z[(i + j) & 7] & z[(i + j + 1) & 7]) ^ z[(i + j + 3) & 7];
+            } else if (MODE >= 2) {
+#pragma unroll
+                for (int j = 0; j < NI; ++j) z[i] = z[i] * z[i] + 1u;                 // not an affine map: cannot be folded
             }
         }
     }
@@ -52,7 +55,7 @@ void run(const char *name, int iters, int warps_per_sm) {
     }
     // warp instructions of the FP64 kind per second, and FMAs per second (a DMMA is 8 x 8 x 4 = 256 FMAs, a DFMA 32)
     const double winstr = (double)grid * warps_per_sm * 8.0 * iters;
-    const double fmas = winstr * ((MODE == 0 || MODE == 2) ? 256.0 : (MODE == 4 ? 0.0 : 32.0));
+    const double fmas = winstr * ((MODE == 0 || MODE == 2) ? 256.0 : ((MODE == 4 || MODE == 6) ? 0.0 : 32.0));
     printf("{\"op\": \"%s\", \"warps_per_sm\": %d, \"int_per_fp64\": %d, \"ms\": %.4f, \"G_fp64_winstr_per_s\": %.2f, \"T_fma_per_s\": %.3f, "
            "\"cycles_per_slot_per_smsp_at_1.93GHz\": %.2f}\n",
            name, warps_per_sm, NI, best, winstr / best * 1e-6, fmas / best * 1e-9,
@@ -74,5 +77,11 @@ int main() {
     run<3, 2>("dfma+int", 4096, 20);
     run<3, 4>("dfma+int", 4096, 20);
     run<4, 2>("int", 4096, 20);
+    run<6, 1>("lop3", 4096, 20);
+    run<6, 4>("lop3", 4096, 20);
+    run<5, 1>("dfma+lop3", 4096, 20);
+    run<5, 2>("dfma+lop3", 4096, 20);
+    run<5, 3>("dfma+lop3", 4096, 20);
+    run<5, 4>("dfma+lop3", 4096, 20);
     return 0;
 }
