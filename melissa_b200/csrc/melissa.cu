@@ -26,6 +26,7 @@
 #include "special.cuh"
 #include "fx128.cuh"
 
+#include <cuda.h>                  // types of the driver's virtual-memory API (multi.cuh); no libcuda at link time
 #include <cuda_runtime.h>
 #include <cub/cub.cuh>
 
@@ -702,7 +703,7 @@ struct HostLap {          // MELISSA_PACK_TIMING set: host-clock laps of the mul
 int g_opt_cell_block = 0;     // 0 = 256 cells
 int g_opt_sliced = -1;        // -1 auto, 0 never, 1 require
 int g_opt_sweep_chunk = 0;    // slices per chunk of the sweep, 0 = from the problem size
-int g_opt_sweep_group = 2;    // consecutive slices a warp claims at a time
+int g_opt_sweep_group = 0;    // consecutive slices a warp claims at a time, 0 = from the chunk size
 int g_opt_sweep_warps = 0;    // warps per CTA of the sweep, 0 = as many as fit
 int g_opt_pack_host = 0;      // 1 = build the slice index with host threads (round 1's builder) instead of on the device
 
@@ -1340,7 +1341,8 @@ int launch_sweep3(melissa_handle *h, bool with_lb) {
     a.chunk_ptr = sl->chunk_ptr; a.stats = sl->stats; a.U = h->U; a.r = h->r;
     a.log_rho_fx = h->log_rho_fx; a.lb_fx = h->lb_fx; a.poison = h->poison;
     a.mills_tab = sl->mills_tab; a.lphi_tab = sl->lphi_tab; a.rbf_tab = sl->rbf_tab; a.rt = sl->rt; a.basis = h->basis;
-    a.K = h->K; a.Tn = sl->Tn; a.NC = sl->NC; a.G = std::max(1, g_opt_sweep_group);
+    a.K = h->K; a.Tn = sl->Tn; a.NC = sl->NC; a.G = g_opt_sweep_group > 0 ? g_opt_sweep_group : (sl->S / std::max(1, sl->NC) < 600 ? 1 : 2);   // short chunks: finer claims
+                                                          // waste less at the chunk-end barrier (-2.5 % on an eighth of C4)
     a.chunk_counter = sl->chunk_counter;
     const int block = 32 * nw;
     const int grid = std::min(h->sm_count, sl->NC);
@@ -1846,7 +1848,7 @@ int melissa_set_option(const char *key, int64_t value) {
         return MELISSA_OK;
     }
     if (!std::strcmp(key, "sweep_group")) {
-        if (value < 1 || value > 64) return fail(MELISSA_ERR_ARG, "sweep_group must be in 1..64");
+        if (value < 0 || value > 64) return fail(MELISSA_ERR_ARG, "sweep_group must be in 0..64 (0 = automatic)");
         g_opt_sweep_group = (int)value;
         return MELISSA_OK;
     }
@@ -2368,7 +2370,18 @@ int melissa_impute_noalloc(int32_t n_cells, int32_t n_regions, int32_t K, int32_
 // ===========================================================================
 // Several GPUs behind one call (multi.cuh)
 // ===========================================================================
+// Fallback when the exchange buffers cannot be shared through the virtual-memory API (multi.cuh): whole-device peer
+// access, switched on for as long as some run needs it and off again afterwards (while it is on, every device
+// allocation of the process is also mapped into the peers).  Links that were already on when the library first
+// looked (another library's doing) are left alone.
+namespace {
+std::mutex g_peer_mu;
+int g_peer_ref[64][64];          // runs using the link dg -> dp
+bool g_peer_ours[64][64];        // the library switched it on (so it switches it off)
+}
+
 struct melissa_multi {
+    std::vector<std::pair<int, int>> links;    // (dg, dp) counted in g_peer_ref
     int G = 0;
     std::vector<melissa_handle *> h;
     std::vector<int64_t> cell_lo;          // first global cell of every shard (G + 1 entries)
@@ -2376,6 +2389,47 @@ struct melissa_multi {
     int64_t N_total = 0;
     double last_loop_ms = 0.0;             // iteration loop of the last run: CUDA events per GPU, max over GPUs
 };
+
+static void peer_links_release(melissa_multi *mm) {
+    std::lock_guard<std::mutex> lock(g_peer_mu);
+    for (const auto &l : mm->links)
+        if (--g_peer_ref[l.first][l.second] == 0 && g_peer_ours[l.first][l.second]) {
+            cudaSetDevice(l.first);
+            cudaDeviceDisablePeerAccess(l.second);
+            cudaGetLastError();
+            g_peer_ours[l.first][l.second] = false;
+        }
+    mm->links.clear();
+}
+
+static int peer_links_acquire(melissa_multi *mm) {
+    for (int g = 0; g < mm->G; ++g)
+        for (int p = 0; p < mm->G; ++p) {
+            const int dg = mm->h[(size_t)g]->device, dp = mm->h[(size_t)p]->device;
+            if (dg == dp) continue;
+            cudaError_t e = cudaSetDevice(dg);
+            if (e == cudaSuccess) {
+                std::lock_guard<std::mutex> lock(g_peer_mu);
+                if (g_peer_ref[dg][dp] == 0) {
+                    e = cudaDeviceEnablePeerAccess(dp, 0);
+                    cudaGetLastError();
+                    if (e == cudaSuccess || e == cudaErrorPeerAccessAlreadyEnabled) {
+                        g_peer_ours[dg][dp] = e == cudaSuccess;
+                        e = cudaSuccess;
+                    }
+                }
+                if (e == cudaSuccess) {
+                    g_peer_ref[dg][dp]++;
+                    mm->links.emplace_back(dg, dp);
+                }
+            }
+            if (e != cudaSuccess) {
+                peer_links_release(mm);
+                return fail(MELISSA_ERR_CUDA, "cudaDeviceEnablePeerAccess(%d -> %d) failed: %s", dg, dp, cudaGetErrorString(e));
+            }
+        }
+    return MELISSA_OK;
+}
 
 int melissa_multi_create(int32_t n_gpus, melissa_handle **handles, melissa_multi **out) {
     if (!out || !handles) return fail(MELISSA_ERR_ARG, "handles / out is NULL");
@@ -2394,7 +2448,7 @@ int melissa_multi_create(int32_t n_gpus, melissa_handle **handles, melissa_multi
         mm->cell_lo.push_back(mm->cell_lo.back() + h->N);
     }
     mm->N_total = mm->cell_lo.back();
-    // every GPU reads every other GPU's partial sums directly
+    // every GPU reads every other GPU's partial sums directly: the links must exist (they are opened per run)
     for (int g = 0; g < n_gpus; ++g) {
         CU(cudaSetDevice(mm->h[g]->device));
         for (int p = 0; p < n_gpus; ++p) {
@@ -2402,13 +2456,8 @@ int melissa_multi_create(int32_t n_gpus, melissa_handle **handles, melissa_multi
             if (dg == dp) continue;
             int can = 0;
             CU(cudaDeviceCanAccessPeer(&can, dg, dp));
-            if (!can) { delete mm; return fail(MELISSA_ERR_CUDA, "GPU %d cannot read GPU %d's memory (no peer access)", dg, dp); }
-            const cudaError_t e = cudaDeviceEnablePeerAccess(dp, 0);
-            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
-                delete mm;
-                return fail(MELISSA_ERR_CUDA, "cudaDeviceEnablePeerAccess(%d -> %d) failed: %s", dg, dp, cudaGetErrorString(e));
-            }
-            cudaGetLastError();
+            if (!can) { melissa_multi_free(mm); return fail(MELISSA_ERR_CUDA, "GPU %d cannot read GPU %d's memory (no peer access)", dg, dp); }
+            if (dg >= 64 || dp >= 64) { melissa_multi_free(mm); return fail(MELISSA_ERR_ARG, "device ordinal beyond 63"); }
         }
     }
     *out = mm;
@@ -2420,6 +2469,7 @@ int melissa_multi_free(melissa_multi *mm) {
     HostLap tm;
     if (mm->own_handles)
         for (melissa_handle *h : mm->h) melissa_free(h);
+    peer_links_release(mm);
     delete mm;
     tm.lap("free");
     return MELISSA_OK;
@@ -2511,7 +2561,7 @@ int melissa_vb_run_multi(melissa_multi *mm, int32_t K, const double *w0, const d
                               delta, alpha, beta, pi_k, lb, lb_cap, n_lb, n_iter, flags);
     struct PerGpu {
         cudaStream_t st = nullptr;
-        double *part[2] = {nullptr, nullptr}, *sum = nullptr, *lbsum = nullptr, *orig_red = nullptr, *orig_lb = nullptr;
+        double *part[2] = {nullptr, nullptr}, *lbpart = nullptr, *sum = nullptr, *lbsum = nullptr, *orig_red = nullptr, *orig_lb = nullptr;
         cudaEvent_t ev_part[2] = {nullptr, nullptr}, ev_lb = nullptr, ev_t0 = nullptr, ev_t1 = nullptr;
         float loop_ms = 0.f;
         int rc = MELISSA_OK;
@@ -2528,6 +2578,25 @@ int melissa_vb_run_multi(melissa_multi *mm, int32_t K, const double *w0, const d
     std::atomic<int> stop{0};
     const melissa_progress_fn progress = g_progress;
     void *const progress_user = g_progress_user;
+    // the memory the peers read: both parities of the partial sums and the bound's two partial terms, one block per GPU
+    static const DrvApi drv;
+    const int64_t n_red_all = (int64_t)mm->h[0]->M * K * mm->h[0]->R + K + 1, part_stride = (n_red_all + 1) & ~(int64_t)1;
+    std::vector<SharedBuf> xbuf((size_t)G);
+    bool shared_ok = true;
+    {
+        int devs[MULTI_MAX_GPUS];
+        for (int g = 0; g < G; ++g) devs[g] = mm->h[(size_t)g]->device;
+        for (int g = 0; g < G && shared_ok; ++g)
+            shared_ok = cudaSetDevice(devs[g]) == cudaSuccess && cudaFree(nullptr) == cudaSuccess &&
+                        xbuf[(size_t)g].alloc(drv, devs[g], (size_t)(2 * part_stride + 8) * sizeof(double), devs, G);
+        if (!shared_ok) {
+            for (SharedBuf &b : xbuf) b.free(drv);
+            cudaGetLastError();
+            const int rc_links = peer_links_acquire(mm);           // whole-device peer access instead
+            if (rc_links) return rc_links;
+        }
+    }
+    tm.lap("run_multi: exchange buffers");
     auto worker = [&](int g) {
         melissa_handle *h = mm->h[(size_t)g];
         PerGpu &me = pg[(size_t)g];
@@ -2546,8 +2615,19 @@ int melissa_vb_run_multi(melissa_multi *mm, int32_t K, const double *w0, const d
         const int64_t n_red = h->red_len;
         me.orig_red = h->red;
         me.orig_lb = h->lbbuf;
-        me.part[0] = h->red;
-        if ((rc = dev_alloc(&me.part[1], n_red)) || (rc = dev_alloc(&me.sum, n_red)) || (rc = dev_alloc(&me.lbsum, 2))) { bad(rc); return; }
+        if (n_red != n_red_all) { bad(fail(MELISSA_ERR_STATE, "GPU %d: unexpected length of the partial sums", h->device)); return; }
+        if (shared_ok) {
+            me.part[0] = reinterpret_cast<double *>(xbuf[(size_t)g].ptr);
+            me.part[1] = me.part[0] + part_stride;
+            me.lbpart = me.part[0] + 2 * part_stride;
+            MG(cudaMemsetAsync(me.lbpart, 0, 2 * sizeof(double), me.st));
+        } else {
+            me.part[0] = h->red;
+            me.lbpart = h->lbbuf;
+            if ((rc = dev_alloc(&me.part[1], n_red))) { bad(rc); return; }
+        }
+        h->lbbuf = me.lbpart;
+        if ((rc = dev_alloc(&me.sum, n_red)) || (rc = dev_alloc(&me.lbsum, 2))) { bad(rc); return; }
         for (int q = 0; q < 2; ++q) MG(cudaEventCreateWithFlags(&me.ev_part[q], cudaEventDisableTiming));
         MG(cudaEventCreateWithFlags(&me.ev_lb, cudaEventDisableTiming));
         MG(cudaEventCreate(&me.ev_t0));
@@ -2580,14 +2660,14 @@ int melissa_vb_run_multi(melissa_multi *mm, int32_t K, const double *w0, const d
                 lp.G = G;
                 for (int p = 0; p < G; ++p) {
                     if (p != g) MG(cudaStreamWaitEvent(me.st, pg[(size_t)p].ev_lb, 0));
-                    lp.p[p] = pg[(size_t)p].orig_lb;
+                    lp.p[p] = pg[(size_t)p].lbpart;
                 }
                 reduce_parts_kernel<<<1, 32, 0, me.st>>>(lp, 2, me.lbsum);
                 h->launches++;
                 h->lbbuf = me.lbsum;
                 double v = 0.0;
                 rc = melissa_vb_lower_bound(h, &v);                 // (synchronises this GPU's stream)
-                h->lbbuf = me.orig_lb;
+                h->lbbuf = me.lbpart;
                 if (rc) { bad(rc); return; }
                 if (!bar.wait()) return;                            // nobody overwrites lbbuf before everybody has read it
                 if (g == 0) {
@@ -2647,7 +2727,8 @@ int melissa_vb_run_multi(melissa_multi *mm, int32_t K, const double *w0, const d
         if (me.st) cudaStreamSynchronize(me.st);
         if (me.orig_red) h->red = me.orig_red;
         if (me.orig_lb) h->lbbuf = me.orig_lb;
-        cudaFree(me.part[1]); cudaFree(me.sum); cudaFree(me.lbsum);
+        if (!shared_ok) cudaFree(me.part[1]);
+        cudaFree(me.sum); cudaFree(me.lbsum);
         for (int q = 0; q < 2; ++q) if (me.ev_part[q]) cudaEventDestroy(me.ev_part[q]);
         if (me.ev_lb) cudaEventDestroy(me.ev_lb);
         if (me.ev_t0) cudaEventDestroy(me.ev_t0);
@@ -2657,6 +2738,8 @@ int melissa_vb_run_multi(melissa_multi *mm, int32_t K, const double *w0, const d
         h->begun = false;
         if (me.st) cudaStreamDestroy(me.st);
     }
+    for (SharedBuf &b : xbuf) b.free(drv);
+    if (!shared_ok) peer_links_release(mm);
     if (rc) return rc;
     const int nlb = (int)lbs.size();
     if (lb) for (int q = 0; q < nlb && q < lb_cap; ++q) lb[q] = lbs[(size_t)q];

@@ -11,6 +11,79 @@
 
 constexpr int MULTI_MAX_GPUS = 16;
 
+// The exchange buffers are the only memory another GPU ever reads, so they alone are made visible to the peers:
+// one block per GPU from the driver's virtual-memory API (cuMemCreate / cuMemMap), opened to every GPU of the job with
+// cuMemSetAccess.  Switching peer access on for whole devices (cudaDeviceEnablePeerAccess) costs far more: it maps
+// every allocation of the device into every peer, once when it is switched on (0.2 s after a C4 pack on 4 GPUs) and
+// again for every later allocation (a pack 3x slower).  The entry points are looked up at run time so that the
+// library has no link-time dependency on libcuda (it must load on a machine without a driver).
+struct DrvApi {
+    CUresult (*GetAllocationGranularity)(size_t *, const CUmemAllocationProp *, CUmemAllocationGranularity_flags) = nullptr;
+    CUresult (*Create)(CUmemGenericAllocationHandle *, size_t, const CUmemAllocationProp *, unsigned long long) = nullptr;
+    CUresult (*AddressReserve)(CUdeviceptr *, size_t, size_t, CUdeviceptr, unsigned long long) = nullptr;
+    CUresult (*Map)(CUdeviceptr, size_t, size_t, CUmemGenericAllocationHandle, unsigned long long) = nullptr;
+    CUresult (*SetAccess)(CUdeviceptr, size_t, const CUmemAccessDesc *, size_t) = nullptr;
+    CUresult (*Unmap)(CUdeviceptr, size_t) = nullptr;
+    CUresult (*AddressFree)(CUdeviceptr, size_t) = nullptr;
+    CUresult (*Release)(CUmemGenericAllocationHandle) = nullptr;
+    bool ok = false;
+    DrvApi() {
+        auto get = [](const char *name, void **fn) {
+            cudaDriverEntryPointQueryResult q;
+            *fn = nullptr;
+            return cudaGetDriverEntryPoint(name, fn, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess && *fn;
+        };
+        ok = get("cuMemGetAllocationGranularity", (void **)&GetAllocationGranularity) && get("cuMemCreate", (void **)&Create) &&
+             get("cuMemAddressReserve", (void **)&AddressReserve) && get("cuMemMap", (void **)&Map) &&
+             get("cuMemSetAccess", (void **)&SetAccess) && get("cuMemUnmap", (void **)&Unmap) &&
+             get("cuMemAddressFree", (void **)&AddressFree) && get("cuMemRelease", (void **)&Release);
+        cudaGetLastError();
+    }
+};
+
+struct SharedBuf {               // device memory of one GPU that the listed GPUs may read and write
+    CUdeviceptr ptr = 0;
+    size_t size = 0;
+    CUmemGenericAllocationHandle hnd = 0;
+    bool created = false, reserved = false, mapped = false;
+    void free(const DrvApi &api) {
+        if (mapped) api.Unmap(ptr, size);
+        if (reserved) api.AddressFree(ptr, size);
+        if (created) api.Release(hnd);
+        *this = SharedBuf();
+    }
+    // false: the caller falls back to whole-device peer access
+    bool alloc(const DrvApi &api, int device, size_t bytes, const int *devices, int n_devices) {
+        if (!api.ok) return false;
+        CUmemAllocationProp prop = {};
+        prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+        prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+        prop.location.id = device;
+        size_t gran = 0;
+        if (api.GetAllocationGranularity(&gran, &prop, CU_MEM_ALLOC_GRANULARITY_MINIMUM) != CUDA_SUCCESS || gran == 0) return false;
+        size = (bytes + gran - 1) / gran * gran;
+        if (api.Create(&hnd, size, &prop, 0) != CUDA_SUCCESS) { *this = SharedBuf(); return false; }
+        created = true;
+        if (api.AddressReserve(&ptr, size, 0, 0, 0) != CUDA_SUCCESS) { free(api); return false; }
+        reserved = true;
+        if (api.Map(ptr, size, 0, hnd, 0) != CUDA_SUCCESS) { free(api); return false; }
+        mapped = true;
+        CUmemAccessDesc acc[MULTI_MAX_GPUS];
+        int n = 0;
+        for (int i = 0; i < n_devices; ++i) {
+            bool seen = false;
+            for (int j = 0; j < n; ++j) seen = seen || acc[j].location.id == devices[i];
+            if (seen) continue;
+            acc[n].location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+            acc[n].location.id = devices[i];
+            acc[n].flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+            ++n;
+        }
+        if (api.SetAccess(ptr, size, acc, (size_t)n) != CUDA_SUCCESS) { free(api); return false; }
+        return true;
+    }
+};
+
 struct PartPtrs {
     const double *p[MULTI_MAX_GPUS];
     int G;
