@@ -37,12 +37,18 @@ def _kmeans(X, K, gen, n_iter=10):
 
 
 def initial_w(engine, data, basis, K, delta_0, alpha_0, beta_0, epsilon_conv, is_kmeans,
-              vb_init_nstart, vb_init_max_iter, rng):
+              vb_init_nstart, vb_init_max_iter, rng, replicas=()):
     """R/melissa_vb.R:134-194.  Keeps the reference's two quirks: the restart
     whose mini-VB ends with the best lower bound contributes its INITIAL w
     (:187-193), and vb_init_nstart == 1 skips the mini-VB (:174-177).
     The per-pair MLE, the N x (M D) profile matrix and the k-means all stay on
-    the GPU; what comes back to the host are K profiles per restart."""
+    the GPU; what comes back to the host are K profiles per restart.
+
+    `replicas`: further Engines that hold the SAME data (normally one per extra GPU).  The restarts' mini-VB runs
+    are independent -- same data, different w0 -- so they are handed out over `engine` and the replicas, one
+    host thread each, no exchange between the GPUs.  The candidates are still drawn in order on `engine`'s GPU
+    and the winner is chosen by the reference's rule in restart order, so the result is the one the sequential
+    loop gives (every run is bit-reproducible)."""
     import torch
     N, M, D = data.N, data.M, int(basis["M"]) + 1
     dev = torch.device(f"cuda:{engine.device}")
@@ -56,8 +62,7 @@ def initial_w(engine, data, basis, K, delta_0, alpha_0, beta_0, epsilon_conv, is
     del w_mle, pc, pr
     W_tmp = X3.view(N, D * M)
     profile = lambda n: X3[int(n)].T.cpu().numpy()                            # ww[, , n]: M x D
-    lb_prev = -1e120
-    optimal_w = None
+    candidates = []
     for _t in range(int(vb_init_nstart)):
         w = np.zeros((M, D, K))
         if is_kmeans:
@@ -73,8 +78,41 @@ def initial_w(engine, data, basis, K, delta_0, alpha_0, beta_0, epsilon_conv, is
                 w[:, :, k] = profile(n)                                       # :171
         if vb_init_nstart == 1:
             return w
-        mini = engine.run(K, w, delta_0, alpha_0, beta_0, max(2, int(vb_init_max_iter)), epsilon_conv)
-        lb_cur = mini["lb"][-1]
+        candidates.append(w)
+    del X3, W_tmp
+    n_it = max(2, int(vb_init_max_iter))
+    mini_lb = lambda eng, w: eng.run(K, w, delta_0, alpha_0, beta_0, n_it, epsilon_conv)["lb"][-1]
+    engines = [engine] + list(replicas)
+    if len(engines) == 1:
+        lbs = [mini_lb(engine, w) for w in candidates]
+    else:
+        import queue
+        import threading
+        todo = queue.SimpleQueue()
+        for t in range(len(candidates)):
+            todo.put(t)
+        lbs, errors = [None] * len(candidates), []
+
+        def work(eng):                                   # (the library call releases the GIL)
+            try:
+                while True:
+                    try:
+                        t = todo.get_nowait()
+                    except queue.Empty:
+                        return
+                    lbs[t] = mini_lb(eng, candidates[t])
+            except Exception as exc:                     # reported below, never swallowed
+                errors.append(exc)
+        threads = [threading.Thread(target=work, args=(e,)) for e in engines]
+        for th in threads:
+            th.start()
+        for th in threads:
+            th.join()
+        if errors:
+            raise errors[0]
+    lb_prev = -1e120
+    optimal_w = None
+    for w, lb_cur in zip(candidates, lbs):               # :187-193, in restart order
         if lb_cur > lb_prev:
             optimal_w, lb_prev = w, lb_cur
     if optimal_w is None:

@@ -116,15 +116,17 @@ def finalize(obj, K, cell_names=None):
 
 def melissa(X, K=3, basis=None, delta_0=None, w=None, alpha_0=.5, beta_0=None, vb_max_iter=300,
             epsilon_conv=1e-5, is_kmeans=True, vb_init_nstart=10, vb_init_max_iter=20,
-            is_parallel=False, no_cores=3, is_verbose=True, device=0, seed=None):
+            is_parallel=False, no_cores=3, is_verbose=True, device=0, seed=None, n_gpus=1):
     """Drop-in for the reference's `melissa()` (R/melissa_vb.R:86-219).
 
     X: the nested list of the reference (list of cells -> list of regions ->
     I x 2 array or None) or a MelissaData.  `is_parallel` / `no_cores` are
     accepted and ignored (the GPU replaces mclapply).  Unlike the reference,
     a user-supplied `w` works (the reference leaves `optimal_w` unassigned in
-    that case, R/melissa_vb.R:134-198).  `device` and `seed` are
-    trailing extras.  Returns a MelissaResult.
+    that case, R/melissa_vb.R:134-198).  `device`, `seed` and `n_gpus`
+    are trailing extras.  With n_gpus > 1 (GPUs device ... device + n_gpus - 1 of one box) the restarts of the
+    default initialisation run as independent replicas, one complete copy of the data per GPU, and the final fit
+    runs on cells sharded over the GPUs (melissa_pack_multi / melissa_vb_run_multi).  Returns a MelissaResult.
     """
     if not (vb_init_nstart > 0):
         raise ValueError("vb_init_nstart not greater than 0")       # assert_that, :93
@@ -138,6 +140,12 @@ def melissa(X, K=3, basis=None, delta_0=None, w=None, alpha_0=.5, beta_0=None, v
     if delta_0 is None:
         delta_0 = np.full(K, .5) + rng.beta(1e-1, 1e1, size=K)      # :110-112
     delta_0 = np.asarray(delta_0, np.float64)
+    n_gpus = int(n_gpus)
+    if n_gpus < 1:
+        raise ValueError("n_gpus must be positive")
+    if n_gpus > 1:
+        return _melissa_several_gpus(data, K, basis, delta_0, w, alpha_0, beta_0, vb_max_iter, epsilon_conv, is_kmeans,
+                                     vb_init_nstart, vb_init_max_iter, is_verbose, list(range(device, device + n_gpus)), rng)
     with Engine(data, basis, device=device, K_hint=K) as eng:
         if w is None:
             from .init import initial_w
@@ -157,6 +165,55 @@ def melissa(X, K=3, basis=None, delta_0=None, w=None, alpha_0=.5, beta_0=None, v
                 obj = melissa_inner(eng, K, optimal_w, delta_0, alpha_0, beta_0, vb_max_iter, epsilon_conv)
         else:
             obj = melissa_inner(eng, K, optimal_w, delta_0, alpha_0, beta_0, vb_max_iter, epsilon_conv)
+    return finalize(obj, K, data.cell_names)
+
+
+def _melissa_several_gpus(data, K, basis, delta_0, w, alpha_0, beta_0, vb_max_iter, epsilon_conv, is_kmeans,
+                          vb_init_nstart, vb_init_max_iter, is_verbose, devices, rng):
+    """melissa() on several GPUs of one box: replicas for the restarts, shards for the fit."""
+    import threading
+
+    from .engine import MultiEngine, progress
+    if w is None:
+        from .init import initial_w
+        n_rep = min(len(devices), int(vb_init_nstart)) if vb_init_nstart > 1 else 1
+        engines, errors = [None] * n_rep, []
+
+        def pack(i):
+            try:
+                engines[i] = Engine(data, basis, device=devices[i], K_hint=K)
+            except Exception as exc:
+                errors.append(exc)
+        threads = [threading.Thread(target=pack, args=(i,)) for i in range(n_rep)]
+        for th in threads:
+            th.start()
+        for th in threads:
+            th.join()
+        try:
+            if errors:
+                raise errors[0]
+            optimal_w = initial_w(engines[0], data, basis, K, delta_0, alpha_0, beta_0, epsilon_conv, is_kmeans,
+                                  vb_init_nstart, vb_init_max_iter, rng, replicas=engines[1:])
+        finally:
+            for e in engines:
+                if e is not None:
+                    e.close()
+    else:
+        optimal_w = np.asarray(w, np.float64)
+    M, D = data.M, int(basis["M"]) + 1
+    with MultiEngine.pack(data, basis, len(devices), devices) as me:
+        if is_verbose:
+            def say(i, lb, diff):
+                if i % 50 == 0:
+                    print(f"\rIt:\t{i}\tLB:\t{lb}\tDiff:\t{diff}")
+                return False
+            with progress(say):
+                obj = me.run(K, optimal_w, delta_0, alpha_0, beta_0, vb_max_iter, epsilon_conv)
+        else:
+            obj = me.run(K, optimal_w, delta_0, alpha_0, beta_0, vb_max_iter, epsilon_conv)
+    _raise_warnings(obj["flags"])
+    b0 = math.sqrt(alpha_0 + M * D / 2.0) if beta_0 is None else beta_0
+    obj.update(basis=basis, delta_0=np.asarray(delta_0, np.float64), alpha_0=alpha_0, beta_0=b0)
     return finalize(obj, K, data.cell_names)
 
 

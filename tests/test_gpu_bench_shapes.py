@@ -180,3 +180,39 @@ def test_progress_hook_is_called_at_every_bound_and_can_stop_the_run(c1):
             cut2 = me.run(2, c1["w0_k2"], c1["k2_delta_0"], vb_max_iter=45, epsilon_conv=0.0)
     assert cut2["n_iter"] == 20 and cut2["flags"] & 4
     np.testing.assert_allclose(cut2["lb"][1:], cut["lb"][1:], rtol=1e-12)
+
+
+def test_restarts_on_replicas_pick_the_start_the_sequential_loop_picks():
+    """Default initialisation with vb_init_nstart mini-VB runs (R/melissa_vb.R:159-194): handed out over two engines
+    that hold the same data (one per GPU when the box has two, else both on GPU 0), the restarts must choose exactly
+    the w the one-engine loop chooses -- the runs are independent and bit-reproducible, the winner is taken in restart
+    order."""
+    import torch
+    from melissa_b200.init import initial_w
+    K = 3
+    d, tr = synth.generate(120, 30, K, n_basis=4, seed=21, sites_per_region=60, cov_lo=0.05, cov_hi=0.3)
+    delta_0 = np.full(K, 0.6)
+    args = dict(K=K, delta_0=delta_0, alpha_0=0.5, beta_0=None, epsilon_conv=1e-5, is_kmeans=True, vb_init_nstart=5,
+                vb_init_max_iter=10)
+    dev2 = 1 if torch.cuda.device_count() > 1 else 0
+    with mb.Engine(d, tr["basis"]) as a, mb.Engine(d, tr["basis"], device=dev2) as b:
+        seq = initial_w(a, d, tr["basis"], rng=np.random.default_rng(4), **args)
+        rep = initial_w(a, d, tr["basis"], rng=np.random.default_rng(4), replicas=[b], **args)
+    assert seq.shape == (30, 5, K) and np.array_equal(seq, rep)
+
+
+def test_melissa_on_two_gpus_gives_the_one_gpu_fit():
+    """melissa(..., n_gpus = 2): restarts as replicas, final fit on cell shards; same start (same seed), so the same fit
+    up to the summation order of the two shards' statistics."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    K = 3
+    d, tr = synth.generate(200, 30, K, n_basis=4, seed=22, sites_per_region=60, cov_lo=0.05, cov_hi=0.3)
+    kw = dict(K=K, basis=tr["basis"], vb_max_iter=40, vb_init_nstart=4, vb_init_max_iter=10, is_verbose=False, seed=9)
+    one = mb.melissa(d, **kw)
+    two = mb.melissa(d, n_gpus=2, **kw)
+    assert np.array_equal(one["labels"], two["labels"])
+    np.testing.assert_allclose(two["lb"][1:], one["lb"][1:], rtol=1e-12)
+    np.testing.assert_allclose(two["W"], one["W"], atol=1e-10)
+    np.testing.assert_allclose(two["r_nk"], one["r_nk"], atol=1e-10)
