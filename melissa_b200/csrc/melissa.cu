@@ -703,6 +703,7 @@ struct HostLap {          // MELISSA_PACK_TIMING set: host-clock laps of the mul
 int g_opt_cell_block = 0;     // 0 = 256 cells
 int g_opt_sliced = -1;        // -1 auto, 0 never, 1 require
 int g_opt_sweep_chunk = 0;    // slices per chunk of the sweep, 0 = from the problem size
+int g_opt_sweep_taper = 0;    // 1 = the three-step chunk list instead of the guided one (comparison)
 int g_opt_sweep_group = 0;    // consecutive slices a warp claims at a time, 0 = from the chunk size
 int g_opt_sweep_warps = 0;    // warps per CTA of the sweep, 0 = as many as fit
 int g_opt_pack_host = 0;      // 1 = build the slice index with host threads (round 1's builder) instead of on the device
@@ -1042,7 +1043,7 @@ int build_slice_index_host(melissa_handle *h, Sliced *sl, const int64_t *pair_pt
             s0 += (int64_t)cbv.size();
         }
     }
-    const std::vector<int32_t> chunk_ptr = make_chunks(blk_first, S, h->sm_count, g_opt_sweep_chunk);
+    const std::vector<int32_t> chunk_ptr = make_chunks(blk_first, S, h->sm_count, g_opt_sweep_chunk, g_opt_sweep_taper != 0);
     sl->NC = (int)chunk_ptr.size() - 1;
     tm.lap("region index");
     // ---- upload, piece by piece
@@ -1341,8 +1342,7 @@ int launch_sweep3(melissa_handle *h, bool with_lb) {
     a.chunk_ptr = sl->chunk_ptr; a.stats = sl->stats; a.U = h->U; a.r = h->r;
     a.log_rho_fx = h->log_rho_fx; a.lb_fx = h->lb_fx; a.poison = h->poison;
     a.mills_tab = sl->mills_tab; a.lphi_tab = sl->lphi_tab; a.rbf_tab = sl->rbf_tab; a.rt = sl->rt; a.basis = h->basis;
-    a.K = h->K; a.Tn = sl->Tn; a.NC = sl->NC; a.G = g_opt_sweep_group > 0 ? g_opt_sweep_group : (sl->S / std::max(1, sl->NC) < 600 ? 1 : 2);   // short chunks: finer claims
-                                                          // waste less at the chunk-end barrier (-2.5 % on an eighth of C4)
+    a.K = h->K; a.Tn = sl->Tn; a.NC = sl->NC; a.G = g_opt_sweep_group > 0 ? g_opt_sweep_group : 2;    // (chunks shorter than 640 slices are claimed slice by slice)
     a.chunk_counter = sl->chunk_counter;
     const int block = 32 * nw;
     const int grid = std::min(h->sm_count, sl->NC);
@@ -1845,6 +1845,10 @@ int melissa_set_option(const char *key, int64_t value) {
     if (!std::strcmp(key, "sweep_chunk")) {
         if (value < 0 || value > (1 << 20)) return fail(MELISSA_ERR_ARG, "sweep_chunk must be in 0..2^20");
         g_opt_sweep_chunk = (int)value;
+        return MELISSA_OK;
+    }
+    if (!std::strcmp(key, "sweep_taper")) {
+        g_opt_sweep_taper = value != 0;
         return MELISSA_OK;
     }
     if (!std::strcmp(key, "sweep_group")) {

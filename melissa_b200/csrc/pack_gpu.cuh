@@ -148,13 +148,18 @@ struct MaxOp {
 };
 
 // Chunks of the sweep: runs of consecutive slices that stay inside one cell block (blk_first[cb] = first slice of
-// block cb, blk_first[NB] = S).  A CTA claims chunks in list order, so the list starts with large chunks (few
-// barriers and flushes) and ends with small ones (the CTAs finish together): full size for the first half of the
-// slices, a half up to 80 %, a quarter after that.
-std::vector<int32_t> make_chunks(const std::vector<int64_t> &blk_first, int64_t S, int sm_count, int chunk_opt) {
+// block cb, blk_first[NB] = S).  A CTA claims chunks in list order and meets at a barrier at the end of each (the
+// block sums are flushed there), where the warps that finished early wait for the last one: about one slice time
+// per chunk.  So chunks should be few and long while there is plenty of work left and short only at the end, where
+// they decide how evenly the CTAs finish: guided self-scheduling, chunk = what is left / (2 x the number of CTAs),
+// between 64 slices and what the limbs can absorb.  (`taper_steps`: the earlier three-step list -- full size for the
+// first half of the slices, a half up to 80 %, a quarter after that -- kept for comparison, option "sweep_taper".)
+std::vector<int32_t> make_chunks(const std::vector<int64_t> &blk_first, int64_t S, int sm_count, int chunk_opt,
+                                 bool taper_steps = false) {
     // (a chunk adds to a shared accumulator at most once per slice; LIMB_MAX_ADDS is what its limbs can absorb)
+    const int64_t cap = 2048;
     const int64_t base = std::min<int64_t>(LIMB_MAX_ADDS, chunk_opt > 0 ? chunk_opt
-                                               : std::max<int64_t>(256, std::min<int64_t>(2048, S / ((int64_t)sm_count * 8))));
+                                               : std::max<int64_t>(256, std::min<int64_t>(cap, S / ((int64_t)sm_count * 8))));
     std::vector<int32_t> chunk_ptr;
     const size_t NB = blk_first.size() - 1;
     for (size_t cb = 0; cb < NB; ++cb) {
@@ -162,9 +167,11 @@ std::vector<int32_t> make_chunks(const std::vector<int64_t> &blk_first, int64_t 
         const int64_t e = blk_first[cb + 1];
         while (q < e) {
             int64_t target = base;
-            if (chunk_opt <= 0) {
+            if (chunk_opt <= 0 && taper_steps) {
                 if (q * 10 >= S * 8) target = std::max<int64_t>(48, base / 4);
                 else if (q * 2 >= S) target = std::max<int64_t>(96, base / 2);
+            } else if (chunk_opt <= 0) {
+                target = std::max<int64_t>(64, std::min<int64_t>(cap, (S - q) / (2 * (int64_t)sm_count)));
             }
             const int64_t left = e - q, pieces = (left + target - 1) / target;
             chunk_ptr.push_back((int32_t)q);
@@ -297,7 +304,7 @@ int build_slice_index_device(melissa_handle *h, Sliced *sl, const int64_t *d_ptr
     sl->x_len = tot[0];
     sl->y_len = tot[1];
     // ---- chunks of the sweep
-    const std::vector<int32_t> chunk_ptr = make_chunks(blk64, S, h->sm_count, sweep_chunk_opt);
+    const std::vector<int32_t> chunk_ptr = make_chunks(blk64, S, h->sm_count, sweep_chunk_opt, g_opt_sweep_taper != 0);
     sl->NC = (int)chunk_ptr.size() - 1;
     if ((rc = dev_alloc(&sl->chunk_ptr, (int64_t)chunk_ptr.size()))) return done(rc);
     CU(cudaMemcpyAsync(sl->chunk_ptr, chunk_ptr.data(), chunk_ptr.size() * 4, cudaMemcpyHostToDevice, st));

@@ -96,9 +96,9 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
     int pre = 0;
     int cur_m = -1;
     int chunk = s_ctl[1];
-    const int G = a.G;
     while (chunk < a.NC) {
         const int c_beg = a.chunk_ptr[chunk], c_end = a.chunk_ptr[chunk + 1];
+        const int G = (c_end - c_beg) < 640 ? 1 : a.G;     // short chunks: single slices, less waiting at the chunk's end
         const int cb = a.slice_cb[c_beg];
         __syncthreads();                                   // everybody has read s_ctl[1]; the last flush is done
         if (threadIdx.x == 0) {
