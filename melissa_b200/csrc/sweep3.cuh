@@ -272,6 +272,10 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
                             const double dt = t - t0;
                             double R0;
                             asm("ld.shared.f64 %0, [%1];" : "=d"(R0) : "r"(mills_addr + ic * 8));
+                            // the bound's table entry is asked for here, a Mills series ahead of its use: ncu had 24 %
+                            // of the bound sweep's samples waiting for it when it was loaded where it is needed
+                            double2 lphi = make_double2(0.0, 0.0);
+                            if (WITH_LB) lphi = __ldg(a.lphi_tab + ic);
                             const double c1 = fma(t0, R0, 1.0);
                             const double c2 = 0.5 * fma(t0, c1, R0);
                             const double c3 = fma(t0, c2, c1) * kInvInt(3);
@@ -295,7 +299,7 @@ __global__ void __launch_bounds__(SWEEP3_THREADS, 1) sweep3_kernel(Sweep3Args a)
                                     // log(Phi(s mu) + 1e-10): both branches of R/melissa_vb.R:471-472 reduce to it; taken
                                     // from its own table on the grid point t0 the E[z] evaluation just used (the table
                                     // is read through L1 / L2: this branch runs on bound iterations only)
-                                    lb_s += fma(0.5 * mu, mu, log_phi_eps(t0, dt, __ldg(a.lphi_tab + ic)));
+                                    lb_s += fma(0.5 * mu, mu, log_phi_eps(t0, dt, lphi));
                                     wrong_s += t < -5.0;
                                 }
                             }
