@@ -92,8 +92,9 @@ int melissa_pack(int32_t n_cells, int32_t n_regions, int64_t n_pairs,
 
 /*
  * Same as melissa_pack, but the five observation arrays are DEVICE pointers on
- * `device` (data generated or already resident there).  x / y are copied device to
- * device; only the index lists visit the host (to be validated and inverted).
+ * `device` (data generated or already resident there).  Nothing visits the host:
+ * the index lists are validated by a kernel (same rules, same messages) and the
+ * layout is built from them on the device.
  * No counterpart in the reference (its data always start as R lists).
  */
 int melissa_pack_device(int32_t n_cells, int32_t n_regions, int64_t n_pairs,
@@ -103,16 +104,26 @@ int melissa_pack_device(int32_t n_cells, int32_t n_regions, int64_t n_pairs,
                         int32_t device, int32_t allow_empty_regions, melissa_handle **out);
 
 /*
- * Library-wide tuning knobs, read by the next melissa_pack*.  No counterpart in the
- * reference.
- *   "cell_block"  cells per block of the sliced layout; 0 (default) = chosen from
- *                 "clusters_hint" so that the sweep keeps three CTAs per SM
- *   "clusters_hint" the K the next fit will most likely use (default 4); only a
- *                 performance hint, any K works with any layout
- *   "sliced"      -1 = use the sliced layout whenever the RBF centres are equally
- *                 spaced (default), 0 = always the flat cell-major layout, 1 = require
- *                 the sliced layout (pack fails if it cannot be used)
- *   "contract_mma" 1 = FP64 tensor-core contraction (default), 0 = CUDA-core contraction
+ * Library-wide tuning and diagnostic knobs; the defaults are what is measured and tested.  No counterpart in
+ * the reference.
+ * Read by the next melissa_pack*:
+ *   "sliced"        -1 = the region-sliced layout whenever the RBF centres are equally spaced (default), 0 = always
+ *                   the flat cell-major layout of round 1, 1 = require the sliced layout (pack fails otherwise)
+ *   "cell_block"    cells per block of the sliced layout; 0 (default) = 256
+ *   "pack_host"     1 = build the slice index with host threads instead of on the device (cross-check of the two builders)
+ *   "sweep_chunk"   slices per chunk of the sweep's work list; 0 (default) = guided self-scheduling from the problem size
+ *   "sweep_taper"   1 = the three-step chunk list (full / half / quarter size) instead of the guided one (comparison)
+ *   "clusters_hint" accepted and ignored (round 1 chose the layout from it)
+ * Read by the next launch:
+ *   "sweep_group"   consecutive slices a warp claims at a time in long chunks (1..64; 0 = default 2); chunks shorter
+ *                   than 640 slices are always claimed slice by slice
+ *   "sweep_warps"   warps per CTA of the sweep; 0 (default) = as many of 20 as fit next to the block sums
+ *   "contract_mma"  1 = FP64 tensor-core contraction (default; K <= 32 and D <= 8), 0 = CUDA-core contraction
+ *   "contract_tma"  1 = its operand staged by cp.async.bulk + mbarrier (default), 0 = plain loads (bit-identical)
+ *   "contract_warps" warps per region of the contraction (1..8; 0 = from the slices per region)
+ *   "debug_estep"   1 = after every sweep a second pair of kernels recomputes every E-step sum from the stored records
+ *                   and every H^T E[z] from x with library exp / erfcx, compares, and prints what differs to stderr
+ *                   (the checker that stood in for compute-sanitizer; slow)
  */
 int melissa_set_option(const char *key, int64_t value);
 
