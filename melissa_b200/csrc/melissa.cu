@@ -2540,11 +2540,19 @@ int melissa_pack_multi(int32_t n_cells, int32_t n_regions, int64_t n_pairs, cons
         });
     for (auto &t : th) t.join();
     tm.lap("pack_multi: shards packed");
-    for (int g = 0; g < n_gpus; ++g)
-        if (rcs[(size_t)g]) {
+    {
+        // a fault in the caller's lists is reported before a CUDA failure of another shard; pair numbers in the
+        // message count from the shard's first pair
+        int bad = -1;
+        for (int g = 0; g < n_gpus && bad < 0; ++g) if (rcs[(size_t)g] == MELISSA_ERR_ARG) bad = g;
+        for (int g = 0; g < n_gpus && bad < 0; ++g) if (rcs[(size_t)g]) bad = g;
+        if (bad >= 0) {
             for (melissa_handle *h : hs) melissa_free(h);
-            return fail(rcs[(size_t)g], "shard %d: %s", g, errs[(size_t)g].c_str());
+            const int c0 = bound[(size_t)bad];
+            return fail(rcs[(size_t)bad], "shard %d (cells from %d, pairs from %lld): %s", bad, c0,
+                        (long long)cell_first[(size_t)c0], errs[(size_t)bad].c_str());
         }
+    }
     // a region no cell of ANY shard covers is an error, as in the single-GPU pack (each shard alone may miss regions)
     int rc = melissa_multi_create(n_gpus, hs.data(), out);
     if (rc) { for (melissa_handle *h : hs) melissa_free(h); return rc; }

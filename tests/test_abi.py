@@ -54,3 +54,27 @@ def test_argument_errors_do_not_need_a_gpu():
                           0, 0, ctypes.byref(h))
     assert rc == 1 and b"RBF" in lib.melissa_last_error()
     assert lib.melissa_vb_phase_a(None) == 3
+
+
+def test_a_fault_in_one_shard_of_melissa_pack_multi_is_named_without_a_gpu():
+    # every shard validates its window of the caller's lists on the host before its first CUDA call; the fault is
+    # reported with the shard and the shard's first cell / pair, ahead of any CUDA failure of another shard
+    import numpy as np
+    from melissa_b200 import _lib
+    lib = _lib.load()
+    n_cells, n_regions = 8, 3
+    cell = np.repeat(np.arange(n_cells, dtype=np.int32), n_regions)
+    reg = np.tile(np.arange(n_regions, dtype=np.int32), n_cells)
+    reg[-2], reg[-1] = 2, 1                                   # cell 7: regions 0, 2, 1 -- not increasing
+    P = cell.size
+    ptr = np.arange(P + 1, dtype=np.int64) * 2
+    x = np.zeros(2 * P)
+    y = np.zeros(2 * P, np.uint8)
+    mus = np.array([-0.5, 0, 0.5])
+    mm = _lib.handle_t()
+    rc = lib.melissa_pack_multi(n_cells, n_regions, P, _lib.ptr(ptr, _lib.c_i64), _lib.ptr(cell, _lib.c_i32),
+                                _lib.ptr(reg, _lib.c_i32), _lib.ptr(x, _lib.c_dbl), _lib.ptr(y, ctypes.c_uint8), 1, 3,
+                                _lib.ptr(mus, _lib.c_dbl), 2.25, 2, None, ctypes.byref(mm))
+    msg = lib.melissa_last_error()
+    assert rc == 1, msg
+    assert b"shard 1 (cells from 4, pairs from 12)" in msg and b"regions must be strictly increasing" in msg and b"pair 11" in msg
