@@ -192,19 +192,29 @@ sell_fill_kernel(const double *__restrict__ x, const uint8_t *__restrict__ y, co
         const int64_t my_src = lane_src[s * 32 + lane], xb = slice_xbase[s], yb = slice_ybase[s];
         for (int i0 = 0; i0 < L; i0 += 32) {
             // rows i0 .. i0 + 31 of every pair of the slice: lane = row while reading, lane = pair while writing
-            for (int l = 0; l < 32; ++l) {
-                const int len = __shfl_sync(0xffffffffu, my_len, l);
-                const int64_t src = __shfl_sync(0xffffffffu, my_src, l);
-                const int i = i0 + lane;
-                double xv = 0.0;
-                uint32_t bit = 0;
-                if (i < len) {
-                    xv = x[src + i];
-                    bit = y[src + i] != 0;
+            // (eight pairs' loads are issued before the first of them is used: the runs are short and scattered,
+            // so it is the number of requests in flight that decides the speed)
+            const int i = i0 + lane;
+            for (int l0 = 0; l0 < 32; l0 += 8) {
+                double xv[8];
+                uint8_t yv[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int len = __shfl_sync(0xffffffffu, my_len, l0 + u);
+                    const int64_t src = __shfl_sync(0xffffffffu, my_src, l0 + u);
+                    xv[u] = 0.0;
+                    yv[u] = 0;
+                    if (i < len) {
+                        xv[u] = __ldg(x + src + i);
+                        yv[u] = __ldg(y + src + i);
+                    }
                 }
-                tile[warp][l][lane] = xv;
-                const uint32_t word = __ballot_sync(0xffffffffu, bit);
-                if (lane == 0) ytile[warp][l] = word;
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    tile[warp][l0 + u][lane] = xv[u];
+                    const uint32_t word = __ballot_sync(0xffffffffu, yv[u] != 0);
+                    if (lane == 0) ytile[warp][l0 + u] = word;
+                }
             }
             __syncwarp();
             const int rows = min(32, L - i0);
