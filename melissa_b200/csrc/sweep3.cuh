@@ -4,13 +4,17 @@
 // What changed against sweep_v2 (round 1) and why:
 //   * ONE persistent CTA per SM.  The two function tables are therefore paid once per SM and can
 //     be finer (truncated-normal table at spacing 1/512 with a 4th-order series, RBF table at a
-//     power-of-two spacing with 6th/5th-order series): 53 FP64 operations per CpG instead of 74.
+//     power-of-two spacing with 6th/5th-order series): 52 FP64 operations per CpG instead of 74.
 //   * The E-step sums of a cell block live in ONE CTA-wide shared array, not one per warp, so
 //     the cell block (= the pool the slices of a region are sorted in) no longer shrinks with K:
 //     256 cells at every K, which takes the row padding at K = 10 from 1.39x to 1.07x.
 //   * The CTA claims CHUNKS (runs of slices inside one cell block) from a global counter, its
 //     warps claim slices of the chunk from a shared counter; the block's sums are flushed to
-//     global memory once per chunk.
+//     global memory once per chunk.  The chunk list is guided self-scheduling (make_chunks,
+//     pack_gpu.cuh): long chunks while much is left, short ones at the end; chunks shorter than
+//     640 slices are claimed slice by slice, so that little is lost at the barrier that ends a chunk.
+//   * WITH_LB: log(Phi(s mu) + 1e-10) comes from a second table (L, L') on the Mills grid and the
+//     recurrence of L' (log_phi_eps, sliced.cuh) instead of one exp and one log per CpG.
 //   * Those sums are accumulated in 128-bit fixed point (integer atomics, fx128.cuh), so the
 //     result does not depend on the order in which warps and CTAs arrive: log rho, and with it
 //     the hard labels (first arg-max, R/melissa_vb.R:212-213), are reproducible bit for bit.
