@@ -1,18 +1,21 @@
 /*
  * .Call glue between R and libmelissa_b200.so.  Written without an R
- * installation at hand: it has never been compiled.  It is the only file that includes R
- * headers; the library itself is R-free.
+ * installation at hand: it has never been compiled against R itself, only type-checked against a
+ * stand-in for the few R declarations it uses (tests/r_stub, tests/test_r_glue.py).  It is the only
+ * file that includes R headers; the library itself is R-free.
  *
  *   R CMD SHLIB melissa_R.c -I../../include -L../../melissa_b200 -lmelissa_b200
  */
 #include <R.h>
 #include <Rinternals.h>
+#include <R_ext/Rdynload.h>
 #include <R_ext/Utils.h>
 #include "melissa_b200.h"
 
 /* User interrupts: R_CheckUserInterrupt() longjmps, which must not happen inside the library (GPU threads are
  * running).  The hook therefore tests for an interrupt inside R_ToplevelExec (no longjmp escapes it) and asks
  * the library to stop; the glue frees the handle and only then raises the R condition. */
+extern void Rf_onintr(void);      /* Rinterface.h on unix-alikes: raises the interrupt condition (after the clean-up) */
 static void check_interrupt(void *unused) { (void) unused; R_CheckUserInterrupt(); }
 static int progress_hook(int32_t iter, double lb, double change, void *verbose) {
     if (*(int *) verbose && iter % 50 == 0)                           /* R/melissa_vb.R:503-507 */
