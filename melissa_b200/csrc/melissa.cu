@@ -2394,6 +2394,13 @@ struct melissa_multi {
     double last_loop_ms = 0.0;             // iteration loop of the last run: CUDA events per GPU, max over GPUs
 };
 
+// The multi-GPU entry points visit every GPU from the calling thread; the caller's current device is put back.
+struct CallerDevice {
+    int prev = -1;
+    CallerDevice() { if (cudaGetDevice(&prev) != cudaSuccess) { prev = -1; cudaGetLastError(); } }
+    ~CallerDevice() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
 static void peer_links_release(melissa_multi *mm) {
     std::lock_guard<std::mutex> lock(g_peer_mu);
     for (const auto &l : mm->links)
@@ -2438,6 +2445,7 @@ static int peer_links_acquire(melissa_multi *mm) {
 int melissa_multi_create(int32_t n_gpus, melissa_handle **handles, melissa_multi **out) {
     if (!out || !handles) return fail(MELISSA_ERR_ARG, "handles / out is NULL");
     if (n_gpus < 1 || n_gpus > MULTI_MAX_GPUS) return fail(MELISSA_ERR_ARG, "n_gpus must be in 1..%d", MULTI_MAX_GPUS);
+    CallerDevice caller_device;
     melissa_multi *mm = new melissa_multi();
     mm->G = n_gpus;
     mm->cell_lo.push_back(0);
@@ -2470,6 +2478,7 @@ int melissa_multi_create(int32_t n_gpus, melissa_handle **handles, melissa_multi
 
 int melissa_multi_free(melissa_multi *mm) {
     if (!mm) return MELISSA_OK;
+    CallerDevice caller_device;
     HostLap tm;
     if (mm->own_handles)
         for (melissa_handle *h : mm->h) melissa_free(h);
@@ -2580,6 +2589,7 @@ int melissa_vb_run_multi(melissa_multi *mm, int32_t K, const double *w0, const d
         std::string err;
     };
     std::vector<PerGpu> pg((size_t)G);
+    CallerDevice caller_device;
     HostLap tm;
     HostBarrier bar;
     bar.n = G;
