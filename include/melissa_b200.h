@@ -195,6 +195,7 @@ int melissa_vb_lb_buffer(melissa_handle *h, void **dev_ptr, int64_t *n_doubles);
  * the library runs one host thread and one stream per GPU; the only per-iteration exchange, the r-weighted
  * sufficient statistics (M K R + K + 1 doubles per GPU), is summed by a kernel on every GPU that reads the other
  * GPUs' partial sums over NVLink peer loads, in rank order (bit-identical on every GPU, no library collective).
+ * These entry points visit every GPU from the calling thread and put its current device back before they return.
  *
  *   melissa_pack_multi    melissa_pack for the whole job: shards the HOST arrays, packs every shard on its GPU
  *                         (devices[g], or GPU g if devices is NULL), returns one object

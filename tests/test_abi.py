@@ -78,3 +78,22 @@ def test_a_fault_in_one_shard_of_melissa_pack_multi_is_named_without_a_gpu():
     msg = lib.melissa_last_error()
     assert rc == 1, msg
     assert b"shard 1 (cells from 4, pairs from 12)" in msg and b"regions must be strictly increasing" in msg and b"pair 11" in msg
+
+
+def test_every_option_the_header_documents_is_accepted_and_every_accepted_one_is_documented():
+    import re
+    from melissa_b200 import _lib
+    lib = _lib.load()
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = open(os.path.join(root, "include", "melissa_b200.h")).read()
+    doc = hdr[hdr.index("Library-wide tuning and diagnostic knobs"):hdr.index("int melissa_set_option")]
+    documented = set(re.findall(r'^ \*   "([a-z_]+)"', doc, re.M))
+    src = open(os.path.join(root, "melissa_b200", "csrc", "melissa.cu")).read()
+    accepted = set(re.findall(r'std::strcmp\(key, "([a-z_]+)"\)', src))
+    assert documented == accepted, (documented ^ accepted)
+    neutral = {"sliced": -1}                                   # the value that means "default" where 0 does not
+    for key in sorted(documented):
+        assert lib.melissa_set_option(key.encode(), neutral.get(key, 0)) == 0, (key, lib.melissa_last_error())
+    lib.melissa_set_option(b"contract_mma", 1)                 # 0 is not the default of these two
+    lib.melissa_set_option(b"contract_tma", 1)
+    assert lib.melissa_set_option(b"no_such_knob", 1) == 1 and b"unknown option" in lib.melissa_last_error()
