@@ -1,5 +1,5 @@
 """Opcode mix of the hottest loop (the backward-branch range with most DFMA) of one kernel (development aid).
-usage: python tools/sass_loop.py <substring of the mangled kernel name> [rows per trip]"""
+usage: python tools/dev/sass_loop.py <substring of the mangled kernel name> [rows per trip]"""
 import collections
 import re
 import subprocess
