@@ -128,3 +128,19 @@ def test_c_restatement_matches_numpy_oracle(c1, c2):
     train = subset(c2, c2["is_train"])
     o = c_oracle.vb_run(train, 4, c2["basis"], c2["w0"], c2["delta_0"], vb_max_iter=20)
     np.testing.assert_allclose(o["lb"][1:], (c2["lb"][1:] + math.log(math.factorial(4)))[:2], rtol=1e-11)
+
+
+@pytest.mark.parametrize("n_basis,K,seed", [(4, 10, 1), (9, 6, 2), (15, 3, 3), (0, 2, 4)])
+def test_c_restatement_matches_numpy_oracle_at_the_shapes_it_checks_the_gpu_at(n_basis, K, seed):
+    """The C restatement is the checker of the GPU tests at the benchmark recipes (K = 10, D = 5) and the timed CPU
+    arm; here it is held against the NumPy oracle at those K / D and at the reference scripts' M = 9 and beyond."""
+    import c_oracle
+    from melissa_b200 import synth
+    d, tr = synth.generate(40, 25, K, n_basis=n_basis, seed=seed, sites_per_region=50, cov_lo=0.1, cov_hi=0.4)
+    delta_0 = np.full(K, 0.6)
+    ref = mo.melissa_inner(d.as_dict(), K, tr["basis"], tr["w0"], delta_0, vb_max_iter=20)
+    got = c_oracle.vb_run(d.as_dict(), K, tr["basis"], tr["w0"], delta_0, vb_max_iter=20, n_threads=2)
+    assert got["n_iter"] == ref["n_iter"] and got["flags"] == ref["flags"]
+    np.testing.assert_allclose(got["lb"][1:], ref["lb"][1:], rtol=1e-11)
+    np.testing.assert_allclose(got["r_nk"], ref["r_nk"], atol=1e-9)
+    np.testing.assert_allclose(got["W"], ref["W"], atol=1e-8)
